@@ -1,0 +1,240 @@
+/*
+ * b200attn.h -- C ABI of the B200-native RadixAttention hot path (libb200attn.so).
+ *
+ * Plain pointers, sizes and a cudaStream_t; no torch types.  Every entry point
+ * returns 0 on success and a negative B200_E* code on failure (the text is
+ * available from b200attn_last_error()).  Nothing here allocates device memory:
+ * workspaces are sized by the *_ints/_floats helpers and owned by the caller, so
+ * every launch is CUDA-graph capturable.
+ *
+ * Reference interfaces each entry point stands in for (paths relative to the
+ * reference tree, python/sglang/...):
+ *   b200attn_store_kv        srt/mem_cache/memory_pool.py:141-192 (_set_kv_buffer_impl),
+ *                            :2305-2381 (MHATokenToKVPool.set_kv_buffer cast/scale/view rules),
+ *                            kernels/ops/kvcache/kvcache.py:57-122 (store_cache),
+ *                            kernels/jit/csrc/elementwise/kvcache.cuh:188-219 (store_kvcache),
+ *                            kernels/jit/csrc/attention/fused_fp8_qkv_kv_cache.cuh:58-90 (fused FP8 variant)
+ *   b200attn_decode_plan     srt/layers/attention/triton_backend.py:304-351 (get_num_kv_splits),
+ *                            :430-446 (_fill_kv_indptr_and_indices),
+ *                            kernels/ops/kvcache/kv_indices.py:8-45 (page-table gather; done in-kernel here)
+ *   b200attn_decode          srt/layers/attention/torch_native_backend.py:176-277 (oracle semantics),
+ *                            kernels/ops/attention/decode_attention.py:968-1044 (decode_attention_fwd:
+ *                            split-KV stage 1 + stage-2 merge)
+ *   b200attn_extend_plan     srt/layers/attention/triton_backend.py:860-900 (qo_indptr / kv_indptr for extend)
+ *   b200attn_extend          srt/layers/attention/torch_native_backend.py:61-174 (oracle semantics),
+ *                            kernels/ops/attention/extend_attention.py:664-812 (extend_attention_fwd)
+ */
+#ifndef B200ATTN_H_
+#define B200ATTN_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200ATTN_ABI_VERSION 1
+
+typedef void* b200_stream_t; /* a cudaStream_t */
+
+/* element types */
+enum {
+  B200_BF16 = 0,
+  B200_F16 = 1,
+  B200_FP8_E4M3 = 2, /* torch.float8_e4m3fn, stored as uint8 in the pool */
+  B200_FP8_E5M2 = 3  /* torch.float8_e5m2 */
+};
+
+/* error codes */
+enum {
+  B200_OK = 0,
+  B200_EINVAL = -1,   /* unsupported shape / dtype / null pointer */
+  B200_ECUDA = -2,    /* a CUDA runtime call failed */
+  B200_ENOTSM100 = -3 /* the device is not compute capability 10.x */
+};
+
+/* kernel selection for b200attn_decode / b200attn_extend */
+enum {
+  B200_KERNEL_AUTO = 0,
+  B200_KERNEL_GENERIC = 1, /* any head_dim <= 512, CUDA-core path */
+  B200_KERNEL_FAST = 2     /* decode: mma + cp.async split-KV; extend: tcgen05/TMEM */
+};
+
+const char* b200attn_last_error(void);
+int b200attn_abi_version(void);
+/* sm_count / cc of the current device */
+int b200attn_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ------------------------------------------------------------------------ *
+ * KV-store scatter:  k_cache[loc[i]] = cast(k[i] / k_scale),  same for V.
+ *   - rows whose loc equals skip_index are not written (slot-0 sink convention of
+ *     store_cache(); pass -1 to write every row like `k_cache[loc] = k`)
+ *   - loc outside [0, size_limit) traps on the device (kvcache.cuh:209)
+ *   - src_dtype == dst_dtype is a byte copy; BF16/F16 -> FP8 is torch's
+ *     round-to-nearest-even, non-saturating cast (|x| > 464 -> NaN for e4m3)
+ *   - k_scale/v_scale != 1: divide in fp32, round to src_dtype, then cast --
+ *     the double rounding of `cache_k.div_(k_scale); cache_k.to(fp8)`
+ * ------------------------------------------------------------------------ */
+typedef struct b200_store_kv_args {
+  const void* k;             /* [num_tokens, k_row_elems] src_dtype */
+  const void* v;             /* [num_tokens, v_row_elems] src_dtype */
+  int64_t k_src_stride;      /* elements between source rows */
+  int64_t v_src_stride;
+  void* k_cache;             /* [slots, k_row_elems] dst_dtype */
+  void* v_cache;
+  int64_t k_cache_stride;    /* elements between slots */
+  int64_t v_cache_stride;
+  const void* loc;           /* [num_tokens] int32 or int64 slot ids */
+  int32_t loc_is_i64;
+  int64_t num_tokens;
+  int32_t k_row_elems;       /* Hkv * Dk */
+  int32_t v_row_elems;       /* Hkv * Dv */
+  int32_t src_dtype;
+  int32_t dst_dtype;
+  float k_scale;             /* 1.0f = none */
+  float v_scale;
+  int64_t size_limit;        /* valid slot ids are [0, size_limit) */
+  int64_t skip_index;        /* -1 = none */
+} b200_store_kv_args;
+
+int b200attn_store_kv(const b200_store_kv_args* args, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------ *
+ * Decode planner.  One tiny launch per forward (graph-capturable): reads
+ * seq_lens on the device and writes the split-KV work list into `plan`:
+ *   plan[0] = chunk_tokens   plan[1] = total_chunks (over all requests)
+ *   plan[2] = batch_size     plan[3] = max_chunks
+ *   plan[8 .. 8+bs]                    chunk_offset[r]  (exclusive scan of chunks per request)
+ *   plan[8+max_bs+1 .. +max_chunks]    chunk_req[c]     (owning request of chunk c)
+ * A work item of the decode kernel is (chunk c, kv head h).
+ * ------------------------------------------------------------------------ */
+int64_t b200attn_decode_plan_ints(int32_t max_bs, int32_t max_chunks);
+
+typedef struct b200_decode_plan_args {
+  const void* seq_lens;      /* [bs] int32 or int64, device */
+  int32_t seq_lens_is_i64;
+  int32_t batch_size;
+  int32_t max_bs;            /* capacity the plan buffer was sized for */
+  int32_t max_chunks;
+  int32_t num_kv_heads;      /* work multiplicity per chunk */
+  int32_t num_ctas;          /* persistent CTAs the decode kernel will run */
+  int32_t waves;             /* target work items per CTA (load-balance granularity) */
+  int32_t min_chunk_tokens;  /* multiple of 64 */
+  int32_t fixed_chunk_tokens;/* > 0 overrides the heuristic (deterministic splits) */
+  int32_t* plan;             /* device, b200attn_decode_plan_ints() ints */
+} b200_decode_plan_args;
+
+int b200attn_decode_plan(const b200_decode_plan_args* args, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------ *
+ * Paged decode attention (one query token per request), split-KV + merge.
+ *   o[r, h, :] = softmax(q[r, h, :] . K[tok(r, 0..L_r)]^T * sm_scale * k_scale) V[...] * v_scale
+ *   tok(r, j) = req_to_token[req_pool_indices[r], j]   (gathered inside the kernel)
+ * ------------------------------------------------------------------------ */
+typedef struct b200_decode_args {
+  const void* q;             /* [bs, Hq, Dk] q_dtype */
+  void* o;                   /* [bs, Hq, Dv] q_dtype */
+  int64_t q_stride_t, q_stride_h;   /* elements */
+  int64_t o_stride_t, o_stride_h;
+  const void* k_cache;       /* [slots, Hkv, Dk] kv_dtype */
+  const void* v_cache;       /* [slots, Hkv, Dv] kv_dtype */
+  int64_t k_stride_s, k_stride_h;   /* elements */
+  int64_t v_stride_s, v_stride_h;
+  const int32_t* req_to_token;      /* [max_reqs+1, max_context_len] */
+  int64_t req_to_token_stride;
+  const void* req_pool_indices;     /* [bs] int32 or int64 */
+  int32_t req_pool_indices_is_i64;
+  const void* seq_lens;             /* [bs] int32 or int64 */
+  int32_t seq_lens_is_i64;
+  int32_t batch_size;
+  int32_t num_q_heads, num_kv_heads;
+  int32_t head_dim_qk, head_dim_v;
+  int32_t q_dtype, kv_dtype;
+  float sm_scale;            /* layer.scaling */
+  float k_scale, v_scale;    /* FP8 descale factors, 1.0f = none */
+  float logit_cap;           /* 0 = off; tanh cap otherwise */
+  const int32_t* plan;       /* written by b200attn_decode_plan on the same stream */
+  int32_t max_bs, max_chunks;
+  float* ws_o;               /* [max_chunks * Hq * Dv] partial outputs */
+  float* ws_lse;             /* [max_chunks * Hq] partial log2-sum-exp */
+  int32_t num_ctas;          /* persistent grid size (same as in the plan) */
+  int32_t kernel;            /* B200_KERNEL_* */
+} b200_decode_args;
+
+int b200attn_decode(const b200_decode_args* args, b200_stream_t stream);
+/* 1 if the fast (mma) decode kernel covers this shape, else 0 */
+int b200attn_decode_fast_supported(int32_t head_dim_qk, int32_t head_dim_v, int32_t group,
+                                   int32_t q_dtype, int32_t kv_dtype);
+/* persistent CTAs per SM the fast decode kernel is tuned for */
+int b200attn_decode_ctas_per_sm(int32_t head_dim, int32_t kv_dtype);
+
+/* ------------------------------------------------------------------------ *
+ * Extend (prefill over a cached prefix) planner: qo_indptr = exclusive scan of
+ * extend_seq_lens and the list of (request, q-tile) work items.
+ *   plan[0] = num_tiles   plan[1] = block_q   plan[2] = batch_size
+ *   plan[8 .. 8+bs]                qo_indptr[r]
+ *   plan[8+max_bs+1 + 2*i + {0,1}] tile i: {request, first q row inside the request}
+ * ------------------------------------------------------------------------ */
+int64_t b200attn_extend_plan_ints(int32_t max_bs, int32_t max_tiles);
+
+typedef struct b200_extend_plan_args {
+  const void* extend_seq_lens;  /* [bs] int32 or int64 */
+  int32_t lens_is_i64;
+  int32_t batch_size;
+  int32_t max_bs;
+  int32_t max_tiles;
+  int32_t block_q;              /* query rows (tokens) per tile */
+  int32_t* plan;
+} b200_extend_plan_args;
+
+int b200attn_extend_plan(const b200_extend_plan_args* args, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------ *
+ * Extend attention.  Query token i of request r (0 <= i < E_r) attends the pool
+ * rows tok(r, 0 .. P_r + i) -- the cached prefix plus the causal part of the new
+ * tokens, which the caller has already stored (store_kv runs first, exactly as
+ * torch_native_backend.py:298-301 does before :312).  causal == 0 attends all
+ * P_r + E_r rows (encoder-only / cross attention).
+ * ------------------------------------------------------------------------ */
+typedef struct b200_extend_args {
+  const void* q;             /* [sum E_r, Hq, Dk] */
+  void* o;                   /* [sum E_r, Hq, Dv] */
+  int64_t q_stride_t, q_stride_h;
+  int64_t o_stride_t, o_stride_h;
+  const void* k_cache;
+  const void* v_cache;
+  int64_t k_stride_s, k_stride_h;
+  int64_t v_stride_s, v_stride_h;
+  const int32_t* req_to_token;
+  int64_t req_to_token_stride;
+  const void* req_pool_indices;
+  int32_t req_pool_indices_is_i64;
+  const void* extend_prefix_lens;   /* [bs] P_r */
+  const void* extend_seq_lens;      /* [bs] E_r */
+  int32_t lens_is_i64;
+  int32_t batch_size;
+  int64_t num_q_tokens;             /* sum E_r (host-known: forward_batch.extend_num_tokens) */
+  int32_t num_q_heads, num_kv_heads;
+  int32_t head_dim_qk, head_dim_v;
+  int32_t q_dtype, kv_dtype;
+  float sm_scale, k_scale, v_scale, logit_cap;
+  int32_t causal;
+  const int32_t* plan;       /* written by b200attn_extend_plan */
+  int32_t max_bs, max_tiles;
+  int32_t num_ctas;
+  int32_t kernel;
+  float* lse;                /* optional [sum E_r, Hq] natural-log LSE output, may be NULL */
+  int64_t pool_slots;        /* rows in k_cache / v_cache (bounds the TMA descriptors) */
+} b200_extend_args;
+
+int b200attn_extend(const b200_extend_args* args, b200_stream_t stream);
+int b200attn_extend_fast_supported(int32_t head_dim_qk, int32_t head_dim_v, int32_t group,
+                                   int32_t q_dtype, int32_t kv_dtype);
+/* query tokens per tile the kernel that would be picked uses (for the plan) */
+int b200attn_extend_block_q(int32_t head_dim_qk, int32_t head_dim_v, int32_t group,
+                            int32_t q_dtype, int32_t kv_dtype, int32_t kernel);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ATTN_H_ */

@@ -1,0 +1,155 @@
+// Shared device/host helpers for libb200attn (sm_100a only).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+
+#include "../../include/b200attn.h"
+
+namespace b200 {
+
+// ---------------------------------------------------------------- host side
+void set_error(const char* fmt, ...);
+
+#define B200_CHECK_ARG(cond, ...)        \
+  do {                                   \
+    if (!(cond)) {                       \
+      ::b200::set_error(__VA_ARGS__);    \
+      return B200_EINVAL;                \
+    }                                    \
+  } while (0)
+
+#define B200_CHECK_CUDA(expr)                                                          \
+  do {                                                                                 \
+    cudaError_t _e = (expr);                                                           \
+    if (_e != cudaSuccess) {                                                           \
+      ::b200::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                        __LINE__);                                                     \
+      return B200_ECUDA;                                                               \
+    }                                                                                  \
+  } while (0)
+
+int sm_count();
+
+// -------------------------------------------------------------- device side
+constexpr int kWarp = 32;
+
+struct e4m3_t { uint8_t x; };
+struct e5m2_t { uint8_t x; };
+
+template <typename T> struct dtype_of;
+template <> struct dtype_of<__nv_bfloat16> { static constexpr int value = B200_BF16; };
+template <> struct dtype_of<__half> { static constexpr int value = B200_F16; };
+template <> struct dtype_of<e4m3_t> { static constexpr int value = B200_FP8_E4M3; };
+template <> struct dtype_of<e5m2_t> { static constexpr int value = B200_FP8_E5M2; };
+
+__device__ __forceinline__ float to_float(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float to_float(__half v) { return __half2float(v); }
+__device__ __forceinline__ float to_float(e4m3_t v) {
+  // e4m3 -> f16 is exact (hardware cvt), f16 -> f32 is exact.
+  uint32_t h2;
+  uint16_t in = v.x;
+  asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(h2) : "h"(in));
+  return __half2float(__ushort_as_half((unsigned short)(h2 & 0xffffu)));
+}
+__device__ __forceinline__ float to_float(e5m2_t v) {
+  // e5m2 is the top byte of an f16.
+  return __half2float(__ushort_as_half((unsigned short)((uint16_t)v.x << 8)));
+}
+
+template <typename T> __device__ __forceinline__ T from_float(float f);
+template <> __device__ __forceinline__ __nv_bfloat16 from_float<__nv_bfloat16>(float f) {
+  return __float2bfloat16_rn(f);
+}
+template <> __device__ __forceinline__ __half from_float<__half>(float f) { return __float2half_rn(f); }
+
+// torch's float -> float8_e4m3fn: round-to-nearest-even, NOT saturating.
+// Everything that would round to the 0x7f encoding (|f| > 464) or is NaN/Inf
+// becomes NaN (0x7f | sign); 464 itself ties to even = 448.
+__device__ __forceinline__ uint8_t float_to_e4m3_bits(float f) {
+  uint32_t b = __float_as_uint(f);
+  const uint32_t sign = b & 0x80000000u;
+  b ^= sign;
+  uint8_t r;
+  if (b >= 0x43F00000u) {  // >= 480, inf, nan
+    r = 0x7f;
+  } else if (b < 0x3C800000u) {  // < 2^-6: subnormal target, add the magic 2^14 .. bias trick
+    const float denorm = __uint_as_float(141u << 23);
+    uint32_t t = __float_as_uint(__uint_as_float(b) + denorm);
+    r = (uint8_t)(t - (141u << 23));
+  } else {
+    const uint32_t odd = (b >> 20) & 1u;
+    b += ((uint32_t)(7 - 127) << 23) + 0x7FFFFu;
+    b += odd;
+    r = (uint8_t)(b >> 20);
+  }
+  return r | (uint8_t)(sign >> 24);
+}
+
+// torch's float -> float8_e5m2 (RNE; overflow -> inf, NaN stays NaN).
+__device__ __forceinline__ uint8_t float_to_e5m2_bits(float f) {
+  uint32_t b = __float_as_uint(f);
+  const uint32_t sign = b & 0x80000000u;
+  b ^= sign;
+  uint8_t r;
+  if (b >= (143u << 23)) {  // >= 65536
+    r = b > (255u << 23) ? 0x7f : 0x7c;
+  } else if (b < (113u << 23)) {  // < 2^-14
+    const float denorm = __uint_as_float(134u << 23);
+    uint32_t t = __float_as_uint(__uint_as_float(b) + denorm);
+    r = (uint8_t)(t - (134u << 23));
+  } else {
+    const uint32_t odd = (b >> 21) & 1u;
+    b += ((uint32_t)(15 - 127) << 23) + 0xFFFFFu;
+    b += odd;
+    r = (uint8_t)(b >> 21);
+  }
+  return r | (uint8_t)(sign >> 24);
+}
+
+template <> __device__ __forceinline__ e4m3_t from_float<e4m3_t>(float f) {
+  return e4m3_t{float_to_e4m3_bits(f)};
+}
+template <> __device__ __forceinline__ e5m2_t from_float<e5m2_t>(float f) {
+  return e5m2_t{float_to_e5m2_bits(f)};
+}
+
+__device__ __forceinline__ int64_t load_index(const void* p, int is_i64, int64_t i) {
+  return is_i64 ? reinterpret_cast<const int64_t*>(p)[i]
+                : (int64_t) reinterpret_cast<const int32_t*>(p)[i];
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fast_tanh(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+// plan buffer layout shared by the planner kernels and their consumers
+constexpr int kPlanHeader = 8;
+
+}  // namespace b200

@@ -1,0 +1,398 @@
+// Paged decode attention for the RadixAttention hot path (sm_100a):
+//   planner  -> split-KV attention (page-table gather inside the kernel) -> split merge
+//
+// Replaces (reference python/sglang/...):
+//   srt/layers/attention/torch_native_backend.py:176-277   per-request gather + SDPA (oracle semantics)
+//   kernels/ops/attention/decode_attention.py:96-281,383-608,731-805  Triton split-KV stage 1/2
+//   kernels/ops/kvcache/kv_indices.py:8-45  + triton_backend.py:304-351  kv_indices gather / num_kv_splits
+//
+// HBM layout read here: K/V pool rows [slot][Hkv][D] (bf16/f16/fp8), page table
+// req_to_token[int32][max_context_len], q [bs][Hq][D].  A work item is (chunk of one
+// request's tokens, kv head); all `group = Hq/Hkv` query heads of that kv head share
+// the single read of the K/V rows.  Algorithmic bytes per launch:
+//   sum_r L_r * Hkv * (Dk + Dv) * s_kv + sum_r L_r * 4 + bs * Hq * (Dk + Dv) * 2.
+#include <type_traits>
+
+#include "common.cuh"
+#include "generic_attn.cuh"
+
+namespace b200 {
+namespace {
+
+// ----------------------------------------------------------------------------
+// planner
+// ----------------------------------------------------------------------------
+struct PlanParams {
+  const void* seq_lens;
+  int32_t* plan;
+  int32_t seq_lens_is_i64, batch_size, max_bs, max_chunks;
+  int32_t num_kv_heads, num_ctas, waves, min_chunk, fixed_chunk;
+};
+
+constexpr int kPlanThreads = 1024;
+
+__device__ __forceinline__ int64_t block_sum_i64(int64_t v, int64_t* s_red) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if (lane == 0) s_red[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    int64_t t = lane < (int)(blockDim.x >> 5) ? s_red[lane] : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (lane == 0) s_red[0] = t;
+  }
+  __syncthreads();
+  const int64_t r = s_red[0];
+  __syncthreads();
+  return r;
+}
+
+__global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanParams p) {
+  __shared__ int64_t s_red[32];
+  __shared__ int32_t s_warp_tot[32];
+  __shared__ int32_t s_chunk, s_carry;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int bs = p.batch_size;
+
+  int64_t local = 0;
+  for (int r = tid; r < bs; r += kPlanThreads) {
+    const int64_t L = load_index(p.seq_lens, p.seq_lens_is_i64, r);
+    local += L > 0 ? L : 0;
+  }
+  const int64_t total = block_sum_i64(local, s_red);
+
+  if (tid == 0) {
+    int64_t chunk;
+    if (p.fixed_chunk > 0) {
+      chunk = p.fixed_chunk;
+    } else {
+      const int64_t target = (int64_t)p.num_ctas * p.waves;
+      chunk = (total * p.num_kv_heads + target - 1) / (target > 0 ? target : 1);
+      if (chunk < p.min_chunk) chunk = p.min_chunk;
+    }
+    chunk = (chunk + 63) / 64 * 64;
+    // capacity: sum_r ceil(L_r / chunk) <= total / chunk + bs must fit the work list
+    while (total / chunk + bs > p.max_chunks && chunk < (int64_t(1) << 30)) chunk *= 2;
+    s_chunk = (int32_t)chunk;
+    s_carry = 0;
+  }
+  __syncthreads();
+  const int chunk = s_chunk;
+
+  int32_t* chunk_offset = p.plan + kPlanHeader;
+  int32_t* chunk_req = p.plan + kPlanHeader + p.max_bs + 1;
+
+  // exclusive scan of chunks-per-request, 1024 requests per pass
+  for (int base = 0; base < bs; base += kPlanThreads) {
+    const int r = base + tid;
+    int32_t n = 0;
+    if (r < bs) {
+      const int64_t L = load_index(p.seq_lens, p.seq_lens_is_i64, r);
+      n = L > 0 ? (int32_t)((L + chunk - 1) / chunk) : 0;
+    }
+    int32_t inc = n;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_warp_tot[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      int32_t w = s_warp_tot[lane];
+      int32_t winc = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int32_t t = __shfl_up_sync(0xffffffffu, winc, o);
+        if (lane >= o) winc += t;
+      }
+      s_warp_tot[lane] = winc - w;  // exclusive warp offsets
+      if (lane == 31) s_red[0] = winc;  // pass total
+    }
+    __syncthreads();
+    const int32_t carry = s_carry;
+    if (r < bs) chunk_offset[r] = carry + s_warp_tot[warp] + inc - n;
+    __syncthreads();
+    if (tid == 0) s_carry = carry + (int32_t)s_red[0];
+    __syncthreads();
+  }
+  const int32_t total_chunks = s_carry;
+  if (tid == 0) {
+    chunk_offset[bs] = total_chunks;
+    p.plan[0] = chunk;
+    p.plan[1] = total_chunks;
+    p.plan[2] = bs;
+    p.plan[3] = p.max_chunks;
+  }
+  __syncthreads();
+  // owner of each chunk: binary search in chunk_offset (block-visible after the barrier)
+  for (int c = tid; c < total_chunks && c < p.max_chunks; c += kPlanThreads) {
+    int lo = 0, hi = bs;  // largest r with chunk_offset[r] <= c
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (chunk_offset[mid] <= c) lo = mid; else hi = mid;
+    }
+    chunk_req[c] = lo;
+  }
+}
+
+// ----------------------------------------------------------------------------
+// shared kernel parameters
+// ----------------------------------------------------------------------------
+struct DecodeParams {
+  const void* q;
+  void* o;
+  const void* k_cache;
+  const void* v_cache;
+  const int32_t* req_to_token;
+  const void* req_pool_indices;
+  const void* seq_lens;
+  const int32_t* plan;
+  float* ws_o;
+  float* ws_lse;
+  int64_t q_stride_t, q_stride_h, o_stride_t, o_stride_h;
+  int64_t k_stride_s, k_stride_h, v_stride_s, v_stride_h;
+  int64_t req_to_token_stride;
+  int32_t req_pool_indices_is_i64, seq_lens_is_i64;
+  int32_t batch_size, num_q_heads, num_kv_heads, group;
+  int32_t head_dim_qk, head_dim_v;
+  int32_t max_bs;
+  float sm_scale, k_scale, v_scale, logit_cap;
+};
+
+struct ChunkInfo {
+  int req;        // batch row
+  int start;      // first token of the chunk inside the request
+  int n_tok;      // tokens in the chunk
+  int n_chunks;   // chunks of this request (1 -> write the final output directly)
+  int64_t pool_row;  // row of req_to_token
+};
+
+__device__ __forceinline__ ChunkInfo load_chunk(const DecodeParams& p, int c) {
+  const int32_t* chunk_offset = p.plan + kPlanHeader;
+  const int32_t* chunk_req = p.plan + kPlanHeader + p.max_bs + 1;
+  ChunkInfo ci;
+  const int chunk = p.plan[0];
+  ci.req = chunk_req[c];
+  const int off = chunk_offset[ci.req];
+  ci.n_chunks = chunk_offset[ci.req + 1] - off;
+  ci.start = (c - off) * chunk;
+  const int64_t L = load_index(p.seq_lens, p.seq_lens_is_i64, ci.req);
+  const int64_t rem = L - ci.start;
+  ci.n_tok = (int)(rem < chunk ? rem : chunk);
+  ci.pool_row = load_index(p.req_pool_indices, p.req_pool_indices_is_i64, ci.req);
+  return ci;
+}
+
+// ----------------------------------------------------------------------------
+// generic kernel: any head_dim <= 512, any dtype pair.  One warp per (chunk, q head).
+// ----------------------------------------------------------------------------
+constexpr int kGenWarps = 4;
+
+template <typename QT, typename KVT>
+__global__ void __launch_bounds__(kGenWarps* kWarp) decode_generic_kernel(const DecodeParams p) {
+  extern __shared__ float smem_f[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* q_s = smem_f + warp * p.head_dim_qk;
+  const int Dk = p.head_dim_qk, Dv = p.head_dim_v, Hq = p.num_q_heads;
+  const int total_chunks = p.plan[1];
+  const int64_t n_items = (int64_t)total_chunks * Hq;
+  const QT* q = reinterpret_cast<const QT*>(p.q);
+  const KVT* kc = reinterpret_cast<const KVT*>(p.k_cache);
+  const KVT* vc = reinterpret_cast<const KVT*>(p.v_cache);
+  const float qk_scale = p.sm_scale * p.k_scale;
+
+  for (int64_t item = (int64_t)blockIdx.x * kGenWarps + warp; item < n_items;
+       item += (int64_t)gridDim.x * kGenWarps) {
+    const int c = (int)(item / Hq), h = (int)(item % Hq);
+    const ChunkInfo ci = load_chunk(p, c);
+    const int kvh = h / p.group;
+    const QT* qrow = q + (int64_t)ci.req * p.q_stride_t + (int64_t)h * p.q_stride_h;
+    __syncwarp();
+    for (int d = lane; d < Dk; d += kWarp) q_s[d] = to_float(qrow[d]);
+    __syncwarp();
+    const int32_t* pt = p.req_to_token + ci.pool_row * p.req_to_token_stride + ci.start;
+
+    RowState st;
+#pragma unroll
+    for (int i = 0; i < kGenAcc; ++i) st.acc[i] = 0.f;
+    attend_row_generic<KVT>(st, q_s, pt, ci.n_tok, kc, vc, p.k_stride_s, p.v_stride_s,
+                            (int64_t)kvh * p.k_stride_h, (int64_t)kvh * p.v_stride_h, Dk, Dv, qk_scale,
+                            p.logit_cap);
+    const float inv_l = 1.f / st.l;
+    if (ci.n_chunks == 1) {
+      QT* orow = reinterpret_cast<QT*>(p.o) + (int64_t)ci.req * p.o_stride_t + (int64_t)h * p.o_stride_h;
+#pragma unroll
+      for (int i = 0; i < kGenAcc; ++i) {
+        const int d = lane + i * kWarp;
+        if (d < Dv) orow[d] = from_float<QT>(st.acc[i] * inv_l * p.v_scale);
+      }
+    } else {
+      float* wo = p.ws_o + ((int64_t)c * Hq + h) * Dv;
+#pragma unroll
+      for (int i = 0; i < kGenAcc; ++i) {
+        const int d = lane + i * kWarp;
+        if (d < Dv) wo[d] = st.acc[i] * inv_l;
+      }
+      if (lane == 0) p.ws_lse[(int64_t)c * Hq + h] = st.m + log2f(st.l);
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------
+// split merge: one warp per (request, q head); requests with a single chunk were
+// already written by the attention kernel.  Also writes zeros for empty requests.
+// ----------------------------------------------------------------------------
+constexpr int kMergeWarps = 4;
+
+template <typename QT>
+__global__ void __launch_bounds__(kMergeWarps* kWarp) decode_merge_kernel(const DecodeParams p) {
+  const int lane = threadIdx.x & 31;
+  const int64_t w = (int64_t)blockIdx.x * kMergeWarps + (threadIdx.x >> 5);
+  const int Hq = p.num_q_heads, Dv = p.head_dim_v;
+  if (w >= (int64_t)p.batch_size * Hq) return;
+  const int r = (int)(w / Hq), h = (int)(w % Hq);
+  const int32_t* chunk_offset = p.plan + kPlanHeader;
+  const int c0 = chunk_offset[r], n = chunk_offset[r + 1] - c0;
+  if (n == 1) return;
+  QT* orow = reinterpret_cast<QT*>(p.o) + (int64_t)r * p.o_stride_t + (int64_t)h * p.o_stride_h;
+  if (n == 0) {
+    for (int d = lane; d < Dv; d += kWarp) orow[d] = from_float<QT>(0.f);
+    return;
+  }
+  float mx = -INFINITY;
+  for (int i = lane; i < n; i += kWarp) mx = fmaxf(mx, p.ws_lse[(int64_t)(c0 + i) * Hq + h]);
+  mx = warp_max(mx);
+  float den = 0.f;
+  for (int i = lane; i < n; i += kWarp) den += exp2f(p.ws_lse[(int64_t)(c0 + i) * Hq + h] - mx);
+  den = warp_sum(den);
+  const float inv = p.v_scale / den;
+  for (int d0 = 0; d0 < Dv; d0 += kWarp) {
+    const int d = d0 + lane;
+    float acc = 0.f;
+    for (int i = 0; i < n; ++i) {
+      const float wgt = exp2f(p.ws_lse[(int64_t)(c0 + i) * Hq + h] - mx);
+      if (d < Dv) acc = fmaf(wgt, p.ws_o[((int64_t)(c0 + i) * Hq + h) * Dv + d], acc);
+    }
+    if (d < Dv) orow[d] = from_float<QT>(acc * inv);
+  }
+}
+
+}  // namespace
+
+// fast path lives in its own translation unit section
+#include "decode_mma.cuh"
+
+namespace {
+
+template <typename QT>
+int launch_generic(const DecodeParams& p, int kv_dtype, int num_ctas, cudaStream_t stream) {
+  const size_t smem = (size_t)kGenWarps * p.head_dim_qk * sizeof(float);
+  const int grid = num_ctas * 8;
+  switch (kv_dtype) {
+    case B200_BF16: decode_generic_kernel<QT, __nv_bfloat16><<<grid, kGenWarps * kWarp, smem, stream>>>(p); break;
+    case B200_F16: decode_generic_kernel<QT, __half><<<grid, kGenWarps * kWarp, smem, stream>>>(p); break;
+    case B200_FP8_E4M3: decode_generic_kernel<QT, e4m3_t><<<grid, kGenWarps * kWarp, smem, stream>>>(p); break;
+    case B200_FP8_E5M2: decode_generic_kernel<QT, e5m2_t><<<grid, kGenWarps * kWarp, smem, stream>>>(p); break;
+    default: set_error("decode: unsupported kv dtype %d", kv_dtype); return B200_EINVAL;
+  }
+  B200_CHECK_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+}  // namespace
+}  // namespace b200
+
+extern "C" int64_t b200attn_decode_plan_ints(int32_t max_bs, int32_t max_chunks) {
+  return (int64_t)b200::kPlanHeader + (int64_t)max_bs + 1 + (int64_t)max_chunks;
+}
+
+extern "C" int b200attn_decode_plan(const b200_decode_plan_args* a, b200_stream_t stream_) {
+  using namespace b200;
+  B200_CHECK_ARG(a && a->seq_lens && a->plan, "decode_plan: null pointer");
+  B200_CHECK_ARG(a->batch_size >= 0 && a->batch_size <= a->max_bs, "decode_plan: bs %d > max_bs %d",
+                 a->batch_size, a->max_bs);
+  B200_CHECK_ARG(a->max_chunks > a->batch_size, "decode_plan: max_chunks %d must exceed bs %d",
+                 a->max_chunks, a->batch_size);
+  B200_CHECK_ARG(a->num_kv_heads > 0 && a->num_ctas > 0 && a->waves > 0, "decode_plan: bad grid hints");
+  B200_CHECK_ARG(a->min_chunk_tokens > 0 && a->min_chunk_tokens % 64 == 0,
+                 "decode_plan: min_chunk_tokens must be a positive multiple of 64");
+  B200_CHECK_ARG(a->fixed_chunk_tokens >= 0, "decode_plan: negative fixed_chunk_tokens");
+  PlanParams p;
+  p.seq_lens = a->seq_lens; p.plan = a->plan; p.seq_lens_is_i64 = a->seq_lens_is_i64;
+  p.batch_size = a->batch_size; p.max_bs = a->max_bs; p.max_chunks = a->max_chunks;
+  p.num_kv_heads = a->num_kv_heads; p.num_ctas = a->num_ctas; p.waves = a->waves;
+  p.min_chunk = a->min_chunk_tokens; p.fixed_chunk = a->fixed_chunk_tokens;
+  decode_plan_kernel<<<1, kPlanThreads, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(p);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+extern "C" int b200attn_decode_fast_supported(int32_t dqk, int32_t dv, int32_t group, int32_t q_dtype,
+                                              int32_t kv_dtype) {
+  return b200::decode_fast_supported(dqk, dv, group, q_dtype, kv_dtype) ? 1 : 0;
+}
+
+extern "C" int b200attn_decode_ctas_per_sm(int32_t head_dim, int32_t kv_dtype) {
+  return b200::decode_fast_ctas_per_sm(head_dim, kv_dtype);
+}
+
+extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_) {
+  using namespace b200;
+  B200_CHECK_ARG(a != nullptr, "decode: null args");
+  if (a->batch_size == 0) return B200_OK;
+  B200_CHECK_ARG(a->q && a->o && a->k_cache && a->v_cache && a->req_to_token && a->req_pool_indices &&
+                     a->seq_lens && a->plan && a->ws_o && a->ws_lse,
+                 "decode: null pointer");
+  B200_CHECK_ARG(a->num_q_heads > 0 && a->num_kv_heads > 0 && a->num_q_heads % a->num_kv_heads == 0,
+                 "decode: Hq=%d must be a multiple of Hkv=%d", a->num_q_heads, a->num_kv_heads);
+  B200_CHECK_ARG(a->head_dim_qk > 0 && a->head_dim_qk <= kGenMaxD && a->head_dim_v > 0 &&
+                     a->head_dim_v <= kGenMaxD,
+                 "decode: head dims (%d, %d) must be in [1, %d]", a->head_dim_qk, a->head_dim_v, kGenMaxD);
+  B200_CHECK_ARG(a->q_dtype == B200_BF16 || a->q_dtype == B200_F16, "decode: q dtype %d", a->q_dtype);
+  B200_CHECK_ARG(a->batch_size <= a->max_bs, "decode: bs %d > max_bs %d", a->batch_size, a->max_bs);
+  B200_CHECK_ARG(a->num_ctas > 0, "decode: num_ctas");
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+
+  DecodeParams p;
+  p.q = a->q; p.o = a->o; p.k_cache = a->k_cache; p.v_cache = a->v_cache;
+  p.req_to_token = a->req_to_token; p.req_pool_indices = a->req_pool_indices; p.seq_lens = a->seq_lens;
+  p.plan = a->plan; p.ws_o = a->ws_o; p.ws_lse = a->ws_lse;
+  p.q_stride_t = a->q_stride_t; p.q_stride_h = a->q_stride_h;
+  p.o_stride_t = a->o_stride_t; p.o_stride_h = a->o_stride_h;
+  p.k_stride_s = a->k_stride_s; p.k_stride_h = a->k_stride_h;
+  p.v_stride_s = a->v_stride_s; p.v_stride_h = a->v_stride_h;
+  p.req_to_token_stride = a->req_to_token_stride;
+  p.req_pool_indices_is_i64 = a->req_pool_indices_is_i64; p.seq_lens_is_i64 = a->seq_lens_is_i64;
+  p.batch_size = a->batch_size; p.num_q_heads = a->num_q_heads; p.num_kv_heads = a->num_kv_heads;
+  p.group = a->num_q_heads / a->num_kv_heads;
+  p.head_dim_qk = a->head_dim_qk; p.head_dim_v = a->head_dim_v; p.max_bs = a->max_bs;
+  p.sm_scale = a->sm_scale; p.k_scale = a->k_scale; p.v_scale = a->v_scale; p.logit_cap = a->logit_cap;
+
+  const bool fast_ok = decode_fast_supported(a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype) &&
+                       decode_fast_layout_ok(p, a->kv_dtype);
+  B200_CHECK_ARG(!(a->kernel == B200_KERNEL_FAST && !fast_ok),
+                 "decode: fast kernel does not cover Dk=%d Dv=%d group=%d q=%d kv=%d (or unaligned strides)",
+                 a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype);
+  const bool use_fast = fast_ok && a->kernel != B200_KERNEL_GENERIC && a->logit_cap == 0.f;
+  int rc;
+  if (use_fast) {
+    rc = launch_decode_fast(p, a->q_dtype, a->kv_dtype, a->num_ctas, stream);
+  } else if (a->q_dtype == B200_BF16) {
+    rc = launch_generic<__nv_bfloat16>(p, a->kv_dtype, a->num_ctas, stream);
+  } else {
+    rc = launch_generic<__half>(p, a->kv_dtype, a->num_ctas, stream);
+  }
+  if (rc != B200_OK) return rc;
+  const int64_t rows = (int64_t)a->batch_size * a->num_q_heads;
+  const unsigned mgrid = (unsigned)((rows + kMergeWarps - 1) / kMergeWarps);
+  if (a->q_dtype == B200_BF16) {
+    decode_merge_kernel<__nv_bfloat16><<<mgrid, kMergeWarps * kWarp, 0, stream>>>(p);
+  } else {
+    decode_merge_kernel<__half><<<mgrid, kMergeWarps * kWarp, 0, stream>>>(p);
+  }
+  B200_CHECK_CUDA(cudaGetLastError());
+  return B200_OK;
+}

@@ -1,0 +1,264 @@
+// Extend (prefill over a cached prefix) attention for the RadixAttention hot path (sm_100a).
+//
+// Replaces (reference python/sglang/...):
+//   srt/layers/attention/torch_native_backend.py:61-174    per-request gather + causal SDPA (oracle semantics)
+//   kernels/ops/attention/extend_attention.py:241-661,664-812  Triton 2-stage extend kernel
+//   srt/layers/attention/triton_backend.py:860-900          qo_indptr / prefix kv_indices metadata
+//
+// Query token i of request r attends pool rows tok(r, 0 .. P_r + i): the new tokens were
+// stored into the pool before this launch, so prefix and new K/V are both read through
+// the page table, exactly like the torch_native oracle.
+// Algorithmic FLOPs per launch: 4 * Hq * D * sum_r (E_r * P_r + E_r * (E_r + 1) / 2).
+#include <type_traits>
+
+#include "common.cuh"
+#include "generic_attn.cuh"
+
+namespace b200 {
+namespace {
+
+// ----------------------------------------------------------------------------
+// planner: qo_indptr (exclusive scan of E_r) + (request, first q row) per q tile.
+// Tiles of one request are listed last-first: under the causal mask the last q tile
+// has the longest KV range, so the persistent kernel starts the heaviest work first.
+// ----------------------------------------------------------------------------
+struct ExtPlanParams {
+  const void* extend_seq_lens;
+  int32_t* plan;
+  int32_t lens_is_i64, batch_size, max_bs, max_tiles, block_q;
+};
+
+constexpr int kPlanThreads = 1024;
+
+__global__ void __launch_bounds__(kPlanThreads) extend_plan_kernel(const ExtPlanParams p) {
+  __shared__ int32_t s_wq[32], s_wt[32];
+  __shared__ int32_t s_carry_q, s_carry_t, s_pass_q, s_pass_t;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int bs = p.batch_size;
+  int32_t* qo_indptr = p.plan + kPlanHeader;
+  int32_t* tiles = p.plan + kPlanHeader + p.max_bs + 1;
+  if (tid == 0) { s_carry_q = 0; s_carry_t = 0; }
+  __syncthreads();
+  for (int base = 0; base < bs; base += kPlanThreads) {
+    const int r = base + tid;
+    int32_t e = 0;
+    if (r < bs) {
+      const int64_t E = load_index(p.extend_seq_lens, p.lens_is_i64, r);
+      e = E > 0 ? (int32_t)E : 0;
+    }
+    const int32_t nt = (e + p.block_q - 1) / p.block_q;
+    int32_t iq = e, it = nt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int32_t a = __shfl_up_sync(0xffffffffu, iq, o);
+      const int32_t b = __shfl_up_sync(0xffffffffu, it, o);
+      if (lane >= o) { iq += a; it += b; }
+    }
+    if (lane == 31) { s_wq[warp] = iq; s_wt[warp] = it; }
+    __syncthreads();
+    if (warp == 0) {
+      const int32_t wq = s_wq[lane], wt = s_wt[lane];
+      int32_t aq = wq, at = wt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int32_t a = __shfl_up_sync(0xffffffffu, aq, o);
+        const int32_t b = __shfl_up_sync(0xffffffffu, at, o);
+        if (lane >= o) { aq += a; at += b; }
+      }
+      s_wq[lane] = aq - wq; s_wt[lane] = at - wt;
+      if (lane == 31) { s_pass_q = aq; s_pass_t = at; }
+    }
+    __syncthreads();
+    const int32_t cq = s_carry_q, ct = s_carry_t;
+    if (r < bs) {
+      const int32_t q0 = cq + s_wq[warp] + iq - e;
+      const int32_t t0 = ct + s_wt[warp] + it - nt;
+      qo_indptr[r] = q0;
+      for (int i = 0; i < nt; ++i) {
+        if (t0 + i < p.max_tiles) {
+          tiles[2 * (t0 + i)] = r;
+          tiles[2 * (t0 + i) + 1] = (nt - 1 - i) * p.block_q;
+        }
+      }
+    }
+    __syncthreads();
+    if (tid == 0) { s_carry_q = cq + s_pass_q; s_carry_t = ct + s_pass_t; }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    qo_indptr[bs] = s_carry_q;
+    p.plan[0] = s_carry_t < p.max_tiles ? s_carry_t : p.max_tiles;
+    p.plan[1] = p.block_q;
+    p.plan[2] = bs;
+    p.plan[3] = s_carry_q;
+  }
+}
+
+struct ExtendParams {
+  const void* q;
+  void* o;
+  const void* k_cache;
+  const void* v_cache;
+  const int32_t* req_to_token;
+  const void* req_pool_indices;
+  const void* extend_prefix_lens;
+  const void* extend_seq_lens;
+  const int32_t* plan;
+  float* lse;
+  int64_t q_stride_t, q_stride_h, o_stride_t, o_stride_h;
+  int64_t k_stride_s, k_stride_h, v_stride_s, v_stride_h;
+  int64_t req_to_token_stride;
+  int64_t num_q_tokens;
+  int32_t req_pool_indices_is_i64, lens_is_i64;
+  int32_t batch_size, num_q_heads, num_kv_heads, group;
+  int32_t head_dim_qk, head_dim_v;
+  int32_t max_bs, causal;
+  float sm_scale, k_scale, v_scale, logit_cap;
+};
+
+// ----------------------------------------------------------------------------
+// generic kernel: one warp per (q token, q head); any head_dim <= 512 / dtype pair.
+// ----------------------------------------------------------------------------
+constexpr int kGenWarps = 4;
+
+template <typename QT, typename KVT>
+__global__ void __launch_bounds__(kGenWarps* kWarp) extend_generic_kernel(const ExtendParams p) {
+  extern __shared__ float smem_f[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* q_s = smem_f + warp * p.head_dim_qk;
+  const int Dk = p.head_dim_qk, Dv = p.head_dim_v, Hq = p.num_q_heads, bs = p.batch_size;
+  const int32_t* qo_indptr = p.plan + kPlanHeader;
+  const int64_t n_rows = (int64_t)qo_indptr[bs] * Hq;
+  const QT* q = reinterpret_cast<const QT*>(p.q);
+  const KVT* kc = reinterpret_cast<const KVT*>(p.k_cache);
+  const KVT* vc = reinterpret_cast<const KVT*>(p.v_cache);
+  const float qk_scale = p.sm_scale * p.k_scale;
+
+  for (int64_t row = (int64_t)blockIdx.x * kGenWarps + warp; row < n_rows;
+       row += (int64_t)gridDim.x * kGenWarps) {
+    const int t = (int)(row / Hq), h = (int)(row % Hq);
+    int lo = 0, hi = bs;  // request owning q token t
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (qo_indptr[mid] <= t) lo = mid; else hi = mid;
+    }
+    const int r = lo, i = t - qo_indptr[r];
+    const int64_t P = load_index(p.extend_prefix_lens, p.lens_is_i64, r);
+    const int64_t E = load_index(p.extend_seq_lens, p.lens_is_i64, r);
+    const int kv_len = (int)(p.causal ? P + i + 1 : P + E);
+    const int64_t pool_row = load_index(p.req_pool_indices, p.req_pool_indices_is_i64, r);
+    const int kvh = h / p.group;
+    const QT* qrow = q + (int64_t)t * p.q_stride_t + (int64_t)h * p.q_stride_h;
+    __syncwarp();
+    for (int d = lane; d < Dk; d += kWarp) q_s[d] = to_float(qrow[d]);
+    __syncwarp();
+    RowState st;
+#pragma unroll
+    for (int j = 0; j < kGenAcc; ++j) st.acc[j] = 0.f;
+    attend_row_generic<KVT>(st, q_s, p.req_to_token + pool_row * p.req_to_token_stride, kv_len, kc, vc,
+                            p.k_stride_s, p.v_stride_s, (int64_t)kvh * p.k_stride_h,
+                            (int64_t)kvh * p.v_stride_h, Dk, Dv, qk_scale, p.logit_cap);
+    const float inv_l = st.l > 0.f ? p.v_scale / st.l : 0.f;
+    QT* orow = reinterpret_cast<QT*>(p.o) + (int64_t)t * p.o_stride_t + (int64_t)h * p.o_stride_h;
+#pragma unroll
+    for (int j = 0; j < kGenAcc; ++j) {
+      const int d = lane + j * kWarp;
+      if (d < Dv) orow[d] = from_float<QT>(st.acc[j] * inv_l);
+    }
+    if (p.lse != nullptr && lane == 0) p.lse[(int64_t)t * Hq + h] = (st.m + log2f(st.l)) * kLn2;
+  }
+}
+
+template <typename QT>
+int launch_generic(const ExtendParams& p, int kv_dtype, int num_ctas, cudaStream_t stream) {
+  const size_t smem = (size_t)kGenWarps * p.head_dim_qk * sizeof(float);
+  const int grid = num_ctas * 8;
+  switch (kv_dtype) {
+    case B200_BF16: extend_generic_kernel<QT, __nv_bfloat16><<<grid, kGenWarps * kWarp, smem, stream>>>(p); break;
+    case B200_F16: extend_generic_kernel<QT, __half><<<grid, kGenWarps * kWarp, smem, stream>>>(p); break;
+    case B200_FP8_E4M3: extend_generic_kernel<QT, e4m3_t><<<grid, kGenWarps * kWarp, smem, stream>>>(p); break;
+    case B200_FP8_E5M2: extend_generic_kernel<QT, e5m2_t><<<grid, kGenWarps * kWarp, smem, stream>>>(p); break;
+    default: set_error("extend: unsupported kv dtype %d", kv_dtype); return B200_EINVAL;
+  }
+  B200_CHECK_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+}  // namespace
+
+#include "extend_tc.cuh"
+
+}  // namespace b200
+
+extern "C" int64_t b200attn_extend_plan_ints(int32_t max_bs, int32_t max_tiles) {
+  return (int64_t)b200::kPlanHeader + (int64_t)max_bs + 1 + 2 * (int64_t)max_tiles;
+}
+
+extern "C" int b200attn_extend_plan(const b200_extend_plan_args* a, b200_stream_t stream_) {
+  using namespace b200;
+  B200_CHECK_ARG(a && a->extend_seq_lens && a->plan, "extend_plan: null pointer");
+  B200_CHECK_ARG(a->batch_size >= 0 && a->batch_size <= a->max_bs, "extend_plan: bs %d > max_bs %d",
+                 a->batch_size, a->max_bs);
+  B200_CHECK_ARG(a->block_q > 0 && a->max_tiles >= 0, "extend_plan: bad block_q/max_tiles");
+  ExtPlanParams p;
+  p.extend_seq_lens = a->extend_seq_lens; p.plan = a->plan; p.lens_is_i64 = a->lens_is_i64;
+  p.batch_size = a->batch_size; p.max_bs = a->max_bs; p.max_tiles = a->max_tiles; p.block_q = a->block_q;
+  extend_plan_kernel<<<1, kPlanThreads, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(p);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+extern "C" int b200attn_extend_fast_supported(int32_t dqk, int32_t dv, int32_t group, int32_t q_dtype,
+                                              int32_t kv_dtype) {
+  return b200::extend_fast_supported(dqk, dv, group, q_dtype, kv_dtype) ? 1 : 0;
+}
+
+extern "C" int b200attn_extend_block_q(int32_t dqk, int32_t dv, int32_t group, int32_t q_dtype,
+                                       int32_t kv_dtype, int32_t kernel) {
+  if (kernel != B200_KERNEL_GENERIC && b200::extend_fast_supported(dqk, dv, group, q_dtype, kv_dtype))
+    return b200::extend_fast_block_q(group);
+  return 64;  // the generic kernel ignores tiles; any value gives a valid plan
+}
+
+extern "C" int b200attn_extend(const b200_extend_args* a, b200_stream_t stream_) {
+  using namespace b200;
+  B200_CHECK_ARG(a != nullptr, "extend: null args");
+  if (a->batch_size == 0 || a->num_q_tokens == 0) return B200_OK;
+  B200_CHECK_ARG(a->q && a->o && a->k_cache && a->v_cache && a->req_to_token && a->req_pool_indices &&
+                     a->extend_prefix_lens && a->extend_seq_lens && a->plan,
+                 "extend: null pointer");
+  B200_CHECK_ARG(a->num_q_heads > 0 && a->num_kv_heads > 0 && a->num_q_heads % a->num_kv_heads == 0,
+                 "extend: Hq=%d must be a multiple of Hkv=%d", a->num_q_heads, a->num_kv_heads);
+  B200_CHECK_ARG(a->head_dim_qk > 0 && a->head_dim_qk <= kGenMaxD && a->head_dim_v > 0 &&
+                     a->head_dim_v <= kGenMaxD,
+                 "extend: head dims (%d, %d) must be in [1, %d]", a->head_dim_qk, a->head_dim_v, kGenMaxD);
+  B200_CHECK_ARG(a->q_dtype == B200_BF16 || a->q_dtype == B200_F16, "extend: q dtype %d", a->q_dtype);
+  B200_CHECK_ARG(a->batch_size <= a->max_bs && a->num_ctas > 0, "extend: bs %d > max_bs %d or num_ctas",
+                 a->batch_size, a->max_bs);
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  ExtendParams p;
+  p.q = a->q; p.o = a->o; p.k_cache = a->k_cache; p.v_cache = a->v_cache;
+  p.req_to_token = a->req_to_token; p.req_pool_indices = a->req_pool_indices;
+  p.extend_prefix_lens = a->extend_prefix_lens; p.extend_seq_lens = a->extend_seq_lens;
+  p.plan = a->plan; p.lse = a->lse;
+  p.q_stride_t = a->q_stride_t; p.q_stride_h = a->q_stride_h;
+  p.o_stride_t = a->o_stride_t; p.o_stride_h = a->o_stride_h;
+  p.k_stride_s = a->k_stride_s; p.k_stride_h = a->k_stride_h;
+  p.v_stride_s = a->v_stride_s; p.v_stride_h = a->v_stride_h;
+  p.req_to_token_stride = a->req_to_token_stride; p.num_q_tokens = a->num_q_tokens;
+  p.req_pool_indices_is_i64 = a->req_pool_indices_is_i64; p.lens_is_i64 = a->lens_is_i64;
+  p.batch_size = a->batch_size; p.num_q_heads = a->num_q_heads; p.num_kv_heads = a->num_kv_heads;
+  p.group = a->num_q_heads / a->num_kv_heads;
+  p.head_dim_qk = a->head_dim_qk; p.head_dim_v = a->head_dim_v; p.max_bs = a->max_bs; p.causal = a->causal;
+  p.sm_scale = a->sm_scale; p.k_scale = a->k_scale; p.v_scale = a->v_scale; p.logit_cap = a->logit_cap;
+
+  const bool fast_ok = extend_fast_supported(a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype) &&
+                       extend_fast_layout_ok(p, a->kv_dtype);
+  B200_CHECK_ARG(!(a->kernel == B200_KERNEL_FAST && !fast_ok),
+                 "extend: fast kernel does not cover Dk=%d Dv=%d group=%d q=%d kv=%d (or unaligned strides)",
+                 a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype);
+  const bool use_fast = fast_ok && a->kernel != B200_KERNEL_GENERIC && a->logit_cap == 0.f;
+  if (use_fast) return launch_extend_fast(p, *a, stream);
+  if (a->q_dtype == B200_BF16) return launch_generic<__nv_bfloat16>(p, a->kv_dtype, a->num_ctas, stream);
+  return launch_generic<__half>(p, a->kv_dtype, a->num_ctas, stream);
+}

@@ -1,0 +1,208 @@
+// KV-store scatter for the token-granular KV pool (sm_100a).
+//
+// Replaces: MHATokenToKVPool.set_kv_buffer -> _set_kv_buffer_impl -> store_cache
+// (reference python/sglang/srt/mem_cache/memory_pool.py:141-192, 2305-2381;
+//  kernels/jit/csrc/elementwise/kvcache.cuh:188-219) and the fused FP8 variant
+// (kernels/jit/csrc/attention/fused_fp8_qkv_kv_cache.cuh:58-90).
+//
+// Layout: one warp moves one 256-element segment of one K row and the matching
+// V row segment; every lane owns 8 consecutive elements = one 16-byte load and one
+// 16-byte (same dtype) or 8-byte (FP8) store.  A CTA of 4 warps therefore covers
+// up to 2 KiB of a bf16 row per row-segment group; the grid is tokens x segments.
+// HBM-bound byte work: algorithmic bytes = T * (Ek + Ev) * (src + dst itemsize) + T * 8.
+#include "common.cuh"
+
+namespace b200 {
+namespace {
+
+constexpr int kStoreWarps = 4;
+constexpr int kVec = 8;                       // elements per lane per segment
+constexpr int kSegElems = kWarp * kVec;       // 256 elements per warp
+
+struct StoreParams {
+  const void* k;
+  const void* v;
+  void* k_cache;
+  void* v_cache;
+  const void* loc;
+  int64_t k_src_stride, v_src_stride, k_cache_stride, v_cache_stride;
+  int64_t num_tokens;
+  int64_t size_limit, skip_index;
+  int32_t k_row_elems, v_row_elems;
+  int32_t k_segs, segs;                        // segments in a K row, K+V segments per token
+  float k_scale, v_scale;
+  int32_t loc_is_i64;
+};
+
+template <typename T> struct Vec8;             // 8 elements of T as one vector register group
+template <> struct Vec8<__nv_bfloat16> { uint4 raw; };
+template <> struct Vec8<__half> { uint4 raw; };
+
+__device__ __forceinline__ uint4 ld_stream_16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_16(void* p, uint4 v) {
+  asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void st_8(void* p, uint2 v) {
+  asm volatile("st.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+
+template <typename SRC> __device__ __forceinline__ float src_bits_to_float(uint16_t b);
+template <> __device__ __forceinline__ float src_bits_to_float<__nv_bfloat16>(uint16_t b) {
+  return __uint_as_float((uint32_t)b << 16);
+}
+template <> __device__ __forceinline__ float src_bits_to_float<__half>(uint16_t b) {
+  return __half2float(__ushort_as_half(b));
+}
+template <typename SRC> __device__ __forceinline__ float round_to_src(float f);
+template <> __device__ __forceinline__ float round_to_src<__nv_bfloat16>(float f) {
+  return __bfloat162float(__float2bfloat16_rn(f));
+}
+template <> __device__ __forceinline__ float round_to_src<__half>(float f) {
+  return __half2float(__float2half_rn(f));
+}
+
+// Convert one source element (as raw 16 bits) to one destination element.
+template <typename SRC, typename DST>
+__device__ __forceinline__ auto convert_elem(uint16_t bits, float scale, bool scaled) {
+  float f = src_bits_to_float<SRC>(bits);
+  if (scaled) f = round_to_src<SRC>(__fdiv_rn(f, scale));  // the pool's in-place div_ in src dtype
+  return from_float<DST>(f);
+}
+
+template <typename SRC, typename DST>
+__device__ __forceinline__ void move_vec8(const SRC* src, DST* dst, float scale, bool scaled) {
+  const uint4 raw = ld_stream_16(src);
+  if constexpr (sizeof(DST) == 2 && dtype_of<SRC>::value == dtype_of<DST>::value) {
+    st_16(dst, raw);  // byte copy
+  } else if constexpr (sizeof(DST) == 1) {
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+    uint32_t out[2] = {0u, 0u};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const uint16_t bits = (uint16_t)(w[i >> 1] >> ((i & 1) * 16));
+      const uint32_t byte = convert_elem<SRC, DST>(bits, scale, scaled).x;
+      out[i >> 2] |= byte << ((i & 3) * 8);
+    }
+    st_8(dst, make_uint2(out[0], out[1]));
+  } else {
+    // 16-bit to a different 16-bit type (bf16 <-> f16)
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+    uint32_t out[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      DST lo = convert_elem<SRC, DST>((uint16_t)(w[i] & 0xffffu), scale, scaled);
+      DST hi = convert_elem<SRC, DST>((uint16_t)(w[i] >> 16), scale, scaled);
+      out[i] = (uint32_t)(*reinterpret_cast<uint16_t*>(&lo)) |
+               ((uint32_t)(*reinterpret_cast<uint16_t*>(&hi)) << 16);
+    }
+    st_16(dst, make_uint4(out[0], out[1], out[2], out[3]));
+  }
+}
+
+template <typename SRC, typename DST>
+__device__ __forceinline__ void move_scalar(const SRC* src, DST* dst, int n, int lane, float scale,
+                                            bool scaled) {
+  for (int i = lane; i < n; i += kWarp) {
+    const uint16_t bits = *reinterpret_cast<const uint16_t*>(src + i);
+    if constexpr (sizeof(DST) == 2 && dtype_of<SRC>::value == dtype_of<DST>::value) {
+      *reinterpret_cast<uint16_t*>(dst + i) = bits;
+    } else {
+      dst[i] = convert_elem<SRC, DST>(bits, scale, scaled);
+    }
+  }
+}
+
+// kVecOK: rows, strides and base pointers are all multiples of 8 elements.
+template <typename SRC, typename DST, bool kVecOK>
+__global__ void __launch_bounds__(kStoreWarps* kWarp) store_kv_kernel(const StoreParams p) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t)blockIdx.x * kStoreWarps + (threadIdx.x >> 5);
+  const int64_t token = warp / p.segs;
+  if (token >= p.num_tokens) return;
+  const int seg = (int)(warp - token * p.segs);
+  const int64_t slot = load_index(p.loc, p.loc_is_i64, token);
+  if (slot == p.skip_index) return;  // reserved sink slot: padded CUDA-graph rows land here
+  if (slot < 0 || slot >= p.size_limit) {
+    if (lane == 0) printf("b200attn store_kv: slot %lld out of [0, %lld)\n", (long long)slot,
+                          (long long)p.size_limit);
+    __trap();
+  }
+  const bool is_v = seg >= p.k_segs;
+  const int s = is_v ? seg - p.k_segs : seg;
+  const int row_elems = is_v ? p.v_row_elems : p.k_row_elems;
+  const SRC* src = reinterpret_cast<const SRC*>(is_v ? p.v : p.k) +
+                   token * (is_v ? p.v_src_stride : p.k_src_stride) + (int64_t)s * kSegElems;
+  DST* dst = reinterpret_cast<DST*>(is_v ? p.v_cache : p.k_cache) +
+             slot * (is_v ? p.v_cache_stride : p.k_cache_stride) + (int64_t)s * kSegElems;
+  const float scale = is_v ? p.v_scale : p.k_scale;
+  const bool scaled = scale != 1.0f;
+  const int remaining = row_elems - s * kSegElems;
+  if constexpr (kVecOK) {
+    if (lane * kVec < remaining) move_vec8<SRC, DST>(src + lane * kVec, dst + lane * kVec, scale, scaled);
+  } else {
+    move_scalar<SRC, DST>(src, dst, remaining < kSegElems ? remaining : kSegElems, lane, scale, scaled);
+  }
+}
+
+template <typename SRC, typename DST>
+int launch_store(const b200_store_kv_args& a, cudaStream_t stream) {
+  StoreParams p;
+  p.k = a.k; p.v = a.v; p.k_cache = a.k_cache; p.v_cache = a.v_cache; p.loc = a.loc;
+  p.k_src_stride = a.k_src_stride; p.v_src_stride = a.v_src_stride;
+  p.k_cache_stride = a.k_cache_stride; p.v_cache_stride = a.v_cache_stride;
+  p.num_tokens = a.num_tokens; p.size_limit = a.size_limit; p.skip_index = a.skip_index;
+  p.k_row_elems = a.k_row_elems; p.v_row_elems = a.v_row_elems;
+  p.k_segs = (a.k_row_elems + kSegElems - 1) / kSegElems;
+  p.segs = p.k_segs + (a.v_row_elems + kSegElems - 1) / kSegElems;
+  p.k_scale = a.k_scale; p.v_scale = a.v_scale; p.loc_is_i64 = a.loc_is_i64;
+  const int64_t warps = a.num_tokens * p.segs;
+  const int64_t blocks = (warps + kStoreWarps - 1) / kStoreWarps;
+  B200_CHECK_ARG(blocks < (int64_t)0x7fffffff, "store_kv: too many rows (%lld)", (long long)a.num_tokens);
+  auto aligned = [](const void* ptr, int64_t bytes) { return ((uintptr_t)ptr % bytes) == 0; };
+  const bool vec_ok = a.k_row_elems % kVec == 0 && a.v_row_elems % kVec == 0 &&
+                      a.k_src_stride % kVec == 0 && a.v_src_stride % kVec == 0 &&
+                      a.k_cache_stride % kVec == 0 && a.v_cache_stride % kVec == 0 &&
+                      aligned(a.k, 16) && aligned(a.v, 16) &&
+                      aligned(a.k_cache, sizeof(DST) * kVec) && aligned(a.v_cache, sizeof(DST) * kVec);
+  if (vec_ok) {
+    store_kv_kernel<SRC, DST, true><<<(unsigned)blocks, kStoreWarps * kWarp, 0, stream>>>(p);
+  } else {
+    store_kv_kernel<SRC, DST, false><<<(unsigned)blocks, kStoreWarps * kWarp, 0, stream>>>(p);
+  }
+  B200_CHECK_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+}  // namespace
+}  // namespace b200
+
+extern "C" int b200attn_store_kv(const b200_store_kv_args* a, b200_stream_t stream_) {
+  using namespace b200;
+  B200_CHECK_ARG(a != nullptr, "store_kv: null args");
+  if (a->num_tokens == 0) return B200_OK;
+  B200_CHECK_ARG(a->k && a->v && a->k_cache && a->v_cache && a->loc, "store_kv: null pointer");
+  B200_CHECK_ARG(a->num_tokens > 0 && a->k_row_elems > 0 && a->v_row_elems > 0,
+                 "store_kv: bad sizes T=%lld Ek=%d Ev=%d", (long long)a->num_tokens, a->k_row_elems,
+                 a->v_row_elems);
+  B200_CHECK_ARG(a->k_scale > 0.f && a->v_scale > 0.f, "store_kv: scales must be positive");
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  const int s = a->src_dtype, d = a->dst_dtype;
+  if (s == B200_BF16 && d == B200_BF16) return launch_store<__nv_bfloat16, __nv_bfloat16>(*a, stream);
+  if (s == B200_F16 && d == B200_F16) return launch_store<__half, __half>(*a, stream);
+  if (s == B200_BF16 && d == B200_F16) return launch_store<__nv_bfloat16, __half>(*a, stream);
+  if (s == B200_F16 && d == B200_BF16) return launch_store<__half, __nv_bfloat16>(*a, stream);
+  if (s == B200_BF16 && d == B200_FP8_E4M3) return launch_store<__nv_bfloat16, e4m3_t>(*a, stream);
+  if (s == B200_F16 && d == B200_FP8_E4M3) return launch_store<__half, e4m3_t>(*a, stream);
+  if (s == B200_BF16 && d == B200_FP8_E5M2) return launch_store<__nv_bfloat16, e5m2_t>(*a, stream);
+  if (s == B200_F16 && d == B200_FP8_E5M2) return launch_store<__half, e5m2_t>(*a, stream);
+  set_error("store_kv: unsupported dtype pair src=%d dst=%d", s, d);
+  return B200_EINVAL;
+}

@@ -1,0 +1,313 @@
+"""Tensor-level entry points over the C ABI (include/b200attn.h).
+
+PyTorch is plumbing here: device memory, the current CUDA stream and dtype tags.
+Every function launches hand-written sm_100a kernels from libb200attn.so on the
+current stream and allocates nothing, so the calls are CUDA-graph capturable.
+There is no CPU path: CPU tensors raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import _C
+
+_DTYPE_CODE = {
+    torch.bfloat16: _C.B200_BF16,
+    torch.float16: _C.B200_F16,
+    torch.float8_e4m3fn: _C.B200_FP8_E4M3,
+    torch.float8_e5m2: _C.B200_FP8_E5M2,
+}
+
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_FAST = _C.KERNEL_AUTO, _C.KERNEL_GENERIC, _C.KERNEL_FAST
+
+# launch counter: bench.py reports it as `gpu_launches`
+launch_count = 0
+
+
+def dtype_code(dtype: torch.dtype) -> int:
+    try:
+        return _DTYPE_CODE[dtype]
+    except KeyError:
+        raise ValueError(f"sglang_b200: unsupported dtype {dtype}") from None
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _need_cuda(*tensors: torch.Tensor) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError(
+                "sglang_b200 ops run only on CUDA tensors (no CPU fallback); got a tensor on " + str(t.device)
+            )
+
+
+def _index_kind(t: torch.Tensor, name: str) -> int:
+    if t.dtype == torch.int64:
+        return 1
+    if t.dtype == torch.int32:
+        return 0
+    raise ValueError(f"{name} must be int32 or int64, got {t.dtype}")
+
+
+_device_info_cache = {}
+
+
+def device_info(device: Optional[torch.device] = None):
+    """(sm_count, cc_major, cc_minor) of the current device; raises unless it is sm_100."""
+    dev = torch.cuda.current_device() if device is None else torch.device(device).index or 0
+    if dev not in _device_info_cache:
+        sm, mj, mn = C.c_int(), C.c_int(), C.c_int()
+        with torch.cuda.device(dev):
+            _C.check(_C.lib.b200attn_device_info(C.byref(sm), C.byref(mj), C.byref(mn)), "device_info")
+        _device_info_cache[dev] = (sm.value, mj.value, mn.value)
+    return _device_info_cache[dev]
+
+
+# --------------------------------------------------------------------------- KV store
+def store_kv(
+    k: torch.Tensor,
+    v: torch.Tensor,
+    k_cache: torch.Tensor,
+    v_cache: torch.Tensor,
+    loc: torch.Tensor,
+    *,
+    cache_dtype: Optional[torch.dtype] = None,
+    k_scale: Optional[float] = None,
+    v_scale: Optional[float] = None,
+    size_limit: int = 0,
+    skip_index: int = 0,
+) -> None:
+    """k_cache[loc[i]] = cast(k[i]), v_cache[loc[i]] = cast(v[i]).
+
+    Mirrors `store_cache` (reference kernels/ops/kvcache/kvcache.py:57-122) plus the
+    cast/scale rules of `MHATokenToKVPool.set_kv_buffer` (memory_pool.py:2339-2349):
+    `cache_dtype` names the logical pool dtype when the buffers are uint8 views of FP8.
+    """
+    global launch_count
+    _need_cuda(k, v, k_cache, v_cache, loc)
+    T = k.shape[0]
+    if T == 0:
+        return
+    k2 = k.reshape(T, -1)
+    v2 = v.reshape(T, -1)
+    if k2.stride(-1) != 1 or v2.stride(-1) != 1:
+        k2, v2 = k2.contiguous(), v2.contiguous()
+    kc = k_cache.view(k_cache.shape[0], -1)
+    vc = v_cache.view(v_cache.shape[0], -1)
+    if cache_dtype is None:
+        cache_dtype = k_cache.dtype
+    if loc.dim() != 1 or loc.shape[0] != T or loc.stride(0) != 1:
+        raise ValueError("loc must be a contiguous 1-D tensor with one slot id per row of k")
+    a = _C.StoreKVArgs(
+        k=k2.data_ptr(), v=v2.data_ptr(), k_src_stride=k2.stride(0), v_src_stride=v2.stride(0),
+        k_cache=kc.data_ptr(), v_cache=vc.data_ptr(), k_cache_stride=kc.stride(0), v_cache_stride=vc.stride(0),
+        loc=loc.data_ptr(), loc_is_i64=_index_kind(loc, "loc"), num_tokens=T,
+        k_row_elems=k2.shape[1], v_row_elems=v2.shape[1],
+        src_dtype=dtype_code(k.dtype), dst_dtype=dtype_code(cache_dtype),
+        k_scale=1.0 if k_scale is None else float(k_scale),
+        v_scale=1.0 if v_scale is None else float(v_scale),
+        size_limit=size_limit if size_limit > 0 else kc.shape[0], skip_index=skip_index,
+    )
+    if kc.shape[1] != k2.shape[1] or vc.shape[1] != v2.shape[1]:
+        raise ValueError(f"row width mismatch: k {tuple(k2.shape)} vs cache {tuple(kc.shape)}")
+    _C.check(_C.lib.b200attn_store_kv(C.byref(a), _stream()), "store_kv")
+    launch_count += 1
+
+
+# --------------------------------------------------------------------------- decode
+@dataclass
+class DecodeWorkspace:
+    """Device buffers whose addresses are baked into CUDA graphs (allocated once)."""
+
+    max_bs: int
+    max_chunks: int
+    num_ctas: int
+    plan: torch.Tensor   # int32
+    ws_o: torch.Tensor   # float32 [max_chunks * Hq * Dv]
+    ws_lse: torch.Tensor  # float32 [max_chunks * Hq]
+
+    @staticmethod
+    def create(max_bs: int, num_q_heads: int, head_dim_v: int, device, *, num_ctas: int,
+               waves: int = 16) -> "DecodeWorkspace":
+        max_chunks = num_ctas * waves * 2 + max_bs + 64
+        n_plan = _C.lib.b200attn_decode_plan_ints(max_bs, max_chunks)
+        return DecodeWorkspace(
+            max_bs=max_bs, max_chunks=max_chunks, num_ctas=num_ctas,
+            plan=torch.zeros(n_plan, dtype=torch.int32, device=device),
+            ws_o=torch.empty(max_chunks * num_q_heads * head_dim_v, dtype=torch.float32, device=device),
+            ws_lse=torch.empty(max_chunks * num_q_heads, dtype=torch.float32, device=device),
+        )
+
+
+def decode_plan(ws: DecodeWorkspace, seq_lens: torch.Tensor, num_kv_heads: int, *, waves: int = 16,
+                min_chunk_tokens: int = 128, fixed_chunk_tokens: int = 0) -> None:
+    """Per-forward split-KV work list, built on the device (no host sync)."""
+    global launch_count
+    _need_cuda(seq_lens, ws.plan)
+    a = _C.DecodePlanArgs(
+        seq_lens=seq_lens.data_ptr(), seq_lens_is_i64=_index_kind(seq_lens, "seq_lens"),
+        batch_size=seq_lens.shape[0], max_bs=ws.max_bs, max_chunks=ws.max_chunks,
+        num_kv_heads=num_kv_heads, num_ctas=ws.num_ctas, waves=waves,
+        min_chunk_tokens=min_chunk_tokens, fixed_chunk_tokens=fixed_chunk_tokens, plan=ws.plan.data_ptr(),
+    )
+    _C.check(_C.lib.b200attn_decode_plan(C.byref(a), _stream()), "decode_plan")
+    launch_count += 1
+
+
+def decode_attention(
+    q: torch.Tensor,            # [bs, Hq, Dk]
+    o: torch.Tensor,            # [bs, Hq, Dv]
+    k_cache: torch.Tensor,      # [slots, Hkv, Dk]
+    v_cache: torch.Tensor,      # [slots, Hkv, Dv]
+    req_to_token: torch.Tensor,
+    req_pool_indices: torch.Tensor,
+    seq_lens: torch.Tensor,
+    ws: DecodeWorkspace,
+    sm_scale: float,
+    *,
+    kv_dtype: Optional[torch.dtype] = None,
+    k_scale: float = 1.0,
+    v_scale: float = 1.0,
+    logit_cap: float = 0.0,
+    kernel: int = KERNEL_AUTO,
+) -> torch.Tensor:
+    global launch_count
+    _need_cuda(q, o, k_cache, v_cache, req_to_token, req_pool_indices, seq_lens)
+    if q.dim() != 3 or o.dim() != 3 or k_cache.dim() != 3 or v_cache.dim() != 3:
+        raise ValueError("decode_attention expects q/o [bs,H,D] and caches [slots,Hkv,D]")
+    if q.stride(2) != 1 or o.stride(2) != 1 or k_cache.stride(2) != 1 or v_cache.stride(2) != 1:
+        raise ValueError("innermost (head_dim) stride must be 1")
+    if req_to_token.dtype != torch.int32:
+        raise ValueError("req_to_token must be int32")
+    bs, Hq, Dk = q.shape
+    Hkv, Dv = k_cache.shape[1], v_cache.shape[2]
+    a = _C.DecodeArgs(
+        q=q.data_ptr(), o=o.data_ptr(),
+        q_stride_t=q.stride(0), q_stride_h=q.stride(1), o_stride_t=o.stride(0), o_stride_h=o.stride(1),
+        k_cache=k_cache.data_ptr(), v_cache=v_cache.data_ptr(),
+        k_stride_s=k_cache.stride(0), k_stride_h=k_cache.stride(1),
+        v_stride_s=v_cache.stride(0), v_stride_h=v_cache.stride(1),
+        req_to_token=req_to_token.data_ptr(), req_to_token_stride=req_to_token.stride(0),
+        req_pool_indices=req_pool_indices.data_ptr(),
+        req_pool_indices_is_i64=_index_kind(req_pool_indices, "req_pool_indices"),
+        seq_lens=seq_lens.data_ptr(), seq_lens_is_i64=_index_kind(seq_lens, "seq_lens"),
+        batch_size=bs, num_q_heads=Hq, num_kv_heads=Hkv, head_dim_qk=Dk, head_dim_v=Dv,
+        q_dtype=dtype_code(q.dtype), kv_dtype=dtype_code(kv_dtype or k_cache.dtype),
+        sm_scale=float(sm_scale), k_scale=float(k_scale), v_scale=float(v_scale), logit_cap=float(logit_cap),
+        plan=ws.plan.data_ptr(), max_bs=ws.max_bs, max_chunks=ws.max_chunks,
+        ws_o=ws.ws_o.data_ptr(), ws_lse=ws.ws_lse.data_ptr(), num_ctas=ws.num_ctas, kernel=kernel,
+    )
+    if ws.ws_o.numel() < ws.max_chunks * Hq * Dv or ws.ws_lse.numel() < ws.max_chunks * Hq:
+        raise ValueError("decode workspace too small for this head configuration")
+    _C.check(_C.lib.b200attn_decode(C.byref(a), _stream()), "decode")
+    launch_count += 2  # attention + merge
+    return o
+
+
+def decode_fast_supported(head_dim_qk: int, head_dim_v: int, group: int, q_dtype, kv_dtype) -> bool:
+    return bool(_C.lib.b200attn_decode_fast_supported(head_dim_qk, head_dim_v, group, dtype_code(q_dtype),
+                                                      dtype_code(kv_dtype)))
+
+
+def decode_ctas_per_sm(head_dim: int, kv_dtype) -> int:
+    return int(_C.lib.b200attn_decode_ctas_per_sm(head_dim, dtype_code(kv_dtype)))
+
+
+# --------------------------------------------------------------------------- extend
+@dataclass
+class ExtendWorkspace:
+    max_bs: int
+    max_tiles: int
+    num_ctas: int
+    plan: torch.Tensor
+
+    @staticmethod
+    def create(max_bs: int, max_tiles: int, device, *, num_ctas: int) -> "ExtendWorkspace":
+        n_plan = _C.lib.b200attn_extend_plan_ints(max_bs, max_tiles)
+        return ExtendWorkspace(max_bs=max_bs, max_tiles=max_tiles, num_ctas=num_ctas,
+                               plan=torch.zeros(n_plan, dtype=torch.int32, device=device))
+
+
+def extend_block_q(head_dim_qk: int, head_dim_v: int, group: int, q_dtype, kv_dtype,
+                   kernel: int = KERNEL_AUTO) -> int:
+    return int(_C.lib.b200attn_extend_block_q(head_dim_qk, head_dim_v, group, dtype_code(q_dtype),
+                                              dtype_code(kv_dtype), kernel))
+
+
+def extend_fast_supported(head_dim_qk: int, head_dim_v: int, group: int, q_dtype, kv_dtype) -> bool:
+    return bool(_C.lib.b200attn_extend_fast_supported(head_dim_qk, head_dim_v, group, dtype_code(q_dtype),
+                                                      dtype_code(kv_dtype)))
+
+
+def extend_plan(ws: ExtendWorkspace, extend_seq_lens: torch.Tensor, block_q: int) -> None:
+    global launch_count
+    _need_cuda(extend_seq_lens, ws.plan)
+    a = _C.ExtendPlanArgs(
+        extend_seq_lens=extend_seq_lens.data_ptr(), lens_is_i64=_index_kind(extend_seq_lens, "extend_seq_lens"),
+        batch_size=extend_seq_lens.shape[0], max_bs=ws.max_bs, max_tiles=ws.max_tiles, block_q=block_q,
+        plan=ws.plan.data_ptr(),
+    )
+    _C.check(_C.lib.b200attn_extend_plan(C.byref(a), _stream()), "extend_plan")
+    launch_count += 1
+
+
+def extend_attention(
+    q: torch.Tensor,            # [T, Hq, Dk]
+    o: torch.Tensor,            # [T, Hq, Dv]
+    k_cache: torch.Tensor,
+    v_cache: torch.Tensor,
+    req_to_token: torch.Tensor,
+    req_pool_indices: torch.Tensor,
+    extend_prefix_lens: torch.Tensor,
+    extend_seq_lens: torch.Tensor,
+    ws: ExtendWorkspace,
+    sm_scale: float,
+    *,
+    kv_dtype: Optional[torch.dtype] = None,
+    k_scale: float = 1.0,
+    v_scale: float = 1.0,
+    logit_cap: float = 0.0,
+    causal: bool = True,
+    kernel: int = KERNEL_AUTO,
+    lse: Optional[torch.Tensor] = None,
+) -> torch.Tensor:
+    global launch_count
+    _need_cuda(q, o, k_cache, v_cache, req_to_token, req_pool_indices, extend_prefix_lens, extend_seq_lens)
+    if q.dim() != 3 or o.dim() != 3 or k_cache.dim() != 3 or v_cache.dim() != 3:
+        raise ValueError("extend_attention expects q/o [T,H,D] and caches [slots,Hkv,D]")
+    if q.stride(2) != 1 or o.stride(2) != 1 or k_cache.stride(2) != 1 or v_cache.stride(2) != 1:
+        raise ValueError("innermost (head_dim) stride must be 1")
+    if req_to_token.dtype != torch.int32:
+        raise ValueError("req_to_token must be int32")
+    if extend_prefix_lens.dtype != extend_seq_lens.dtype:
+        raise ValueError("extend_prefix_lens and extend_seq_lens must share a dtype")
+    T, Hq, Dk = q.shape
+    Hkv, Dv = k_cache.shape[1], v_cache.shape[2]
+    a = _C.ExtendArgs(
+        q=q.data_ptr(), o=o.data_ptr(),
+        q_stride_t=q.stride(0), q_stride_h=q.stride(1), o_stride_t=o.stride(0), o_stride_h=o.stride(1),
+        k_cache=k_cache.data_ptr(), v_cache=v_cache.data_ptr(),
+        k_stride_s=k_cache.stride(0), k_stride_h=k_cache.stride(1),
+        v_stride_s=v_cache.stride(0), v_stride_h=v_cache.stride(1),
+        req_to_token=req_to_token.data_ptr(), req_to_token_stride=req_to_token.stride(0),
+        req_pool_indices=req_pool_indices.data_ptr(),
+        req_pool_indices_is_i64=_index_kind(req_pool_indices, "req_pool_indices"),
+        extend_prefix_lens=extend_prefix_lens.data_ptr(), extend_seq_lens=extend_seq_lens.data_ptr(),
+        lens_is_i64=_index_kind(extend_seq_lens, "extend_seq_lens"),
+        batch_size=extend_seq_lens.shape[0], num_q_tokens=T,
+        num_q_heads=Hq, num_kv_heads=Hkv, head_dim_qk=Dk, head_dim_v=Dv,
+        q_dtype=dtype_code(q.dtype), kv_dtype=dtype_code(kv_dtype or k_cache.dtype),
+        sm_scale=float(sm_scale), k_scale=float(k_scale), v_scale=float(v_scale), logit_cap=float(logit_cap),
+        causal=1 if causal else 0, plan=ws.plan.data_ptr(), max_bs=ws.max_bs, max_tiles=ws.max_tiles,
+        num_ctas=ws.num_ctas, kernel=kernel, lse=0 if lse is None else lse.data_ptr(),
+        pool_slots=k_cache.shape[0],
+    )
+    _C.check(_C.lib.b200attn_extend(C.byref(a), _stream()), "extend")
+    launch_count += 1
+    return o

@@ -1,0 +1,120 @@
+"""Shared test helpers: golden-fixture decoding and construction of the backend over mirror pools."""
+from __future__ import annotations
+
+from pathlib import Path
+from types import SimpleNamespace
+
+import numpy as np
+import torch
+
+GOLDEN = Path(__file__).resolve().parent / "golden"
+DTYPES = {0: torch.bfloat16, 1: torch.float16, 2: torch.float8_e4m3fn, 3: torch.float8_e5m2, 4: torch.float32}
+
+# BF16 tolerance of BASELINE.json's north_star: max-abs <= 2e-2 against the FP32-accumulated oracle
+ATOL = 2e-2
+
+
+def from_bits(a: np.ndarray, dtype: torch.dtype) -> torch.Tensor:
+    """Inverse of oracle/gen_golden.py:bits()."""
+    if dtype in (torch.bfloat16, torch.float16):
+        return torch.from_numpy(a.view(np.int16).copy()).view(dtype)
+    if dtype in (torch.float8_e4m3fn, torch.float8_e5m2):
+        return torch.from_numpy(a.copy())  # pools keep FP8 as uint8 (store_dtype)
+    return torch.from_numpy(a.copy())
+
+
+class GoldenAttention:
+    def __init__(self):
+        self.z = np.load(GOLDEN / "attention.npz")
+        self.names = [str(n) for n in self.z["names"]]
+
+    def case(self, name: str) -> SimpleNamespace:
+        z = self.z
+        meta = z[f"{name}.meta"]
+        c = SimpleNamespace(name=name)
+        c.is_decode = bool(meta[0])
+        c.dtype, c.pool_dtype = DTYPES[int(meta[1])], DTYPES[int(meta[2])]
+        c.Hq, c.Hkv, c.D, c.page_size, c.pool_rows = (int(x) for x in meta[3:8])
+        c.prefix_lens = [int(x) for x in z[f"{name}.prefix_lens"]]
+        c.extend_lens = [int(x) for x in z[f"{name}.extend_lens"]]
+        c.seq_lens = [p + e for p, e in zip(c.prefix_lens, c.extend_lens)]
+        c.req_to_token = torch.from_numpy(z[f"{name}.req_to_token"].copy())
+        c.req_pool_indices = torch.from_numpy(z[f"{name}.req_pool_indices"].copy())
+        c.out_cache_loc = torch.from_numpy(z[f"{name}.out_cache_loc"].copy())
+        c.q = from_bits(z[f"{name}.q"], c.dtype)
+        c.k_new = from_bits(z[f"{name}.k_new"], c.dtype)
+        c.v_new = from_bits(z[f"{name}.v_new"], c.dtype)
+        c.k_pool = from_bits(z[f"{name}.k_pool"], c.pool_dtype)
+        c.v_pool = from_bits(z[f"{name}.v_pool"], c.pool_dtype)
+        c.k_rows_after = from_bits(z[f"{name}.k_rows_after"], c.pool_dtype)
+        c.v_rows_after = from_bits(z[f"{name}.v_rows_after"], c.pool_dtype)
+        c.out_ref = from_bits(z[f"{name}.out_ref"], c.dtype)
+        c.out_ref_fp32 = torch.from_numpy(z[f"{name}.out_ref_fp32"].copy())
+        return c
+
+
+def store_dtype(dtype: torch.dtype) -> torch.dtype:
+    return torch.uint8 if dtype in (torch.float8_e4m3fn, torch.float8_e5m2) else dtype
+
+
+def make_runner(*, device, dtype, pool_dtype, Hq, Hkv, D, page_size, pool_rows, max_bs, max_context_len,
+                layer_num=1, v_head_dim=None):
+    """A minimal model runner over the mirror pools (what MockModelRunner provides in the reference kit,
+    test/kits/attention_unittest/attention_methods/dense_attention.py:306-418)."""
+    from sglang_b200.srt_mirror import MHATokenToKVPool, ReqToTokenPool
+
+    rtp = ReqToTokenPool(size=max_bs, max_context_len=max_context_len, device=device)
+    pool = MHATokenToKVPool(size=pool_rows - page_size, page_size=page_size, dtype=pool_dtype, head_num=Hkv,
+                            head_dim=D, layer_num=layer_num, device=device, v_head_dim=v_head_dim)
+    cfg = SimpleNamespace(
+        num_attention_heads=Hq, num_key_value_heads=Hkv, head_dim=D, context_len=max_context_len,
+        get_num_kv_heads=lambda tp: Hkv // tp, get_max_num_attention_heads=lambda: Hq,
+    )
+    return SimpleNamespace(device=device, dtype=dtype, page_size=page_size, model_config=cfg,
+                           req_to_token_pool=rtp, token_to_kv_pool=pool, sliding_window_size=None)
+
+
+def make_forward_batch(c, device):
+    from sglang_b200.srt_mirror import ForwardBatch, ForwardMode
+
+    bs = len(c.seq_lens)
+    fb = ForwardBatch(
+        forward_mode=ForwardMode.DECODE if c.is_decode else ForwardMode.EXTEND,
+        batch_size=bs,
+        req_pool_indices=c.req_pool_indices.to(device),
+        seq_lens=torch.tensor(c.seq_lens, dtype=torch.int32, device=device),
+        seq_lens_cpu=torch.tensor(c.seq_lens, dtype=torch.int32),
+        out_cache_loc=c.out_cache_loc.to(device),
+        seq_lens_sum=sum(c.seq_lens),
+    )
+    if not c.is_decode:
+        fb.extend_prefix_lens = torch.tensor(c.prefix_lens, dtype=torch.int32, device=device)
+        fb.extend_prefix_lens_cpu = list(c.prefix_lens)
+        fb.extend_seq_lens = torch.tensor(c.extend_lens, dtype=torch.int32, device=device)
+        fb.extend_seq_lens_cpu = list(c.extend_lens)
+        fb.extend_num_tokens = sum(c.extend_lens)
+    return fb
+
+
+def run_backend_on_case(c, device="cuda", decode_kernel=0, extend_kernel=0):
+    """Golden case -> B200AttnBackend over mirror pools -> (output [T, Hq*D], pool)."""
+    from sglang_b200.backend import B200AttnBackend
+    from sglang_b200.srt_mirror import RadixAttention
+
+    runner = make_runner(device=device, dtype=c.dtype, pool_dtype=c.pool_dtype, Hq=c.Hq, Hkv=c.Hkv, D=c.D,
+                         page_size=c.page_size, pool_rows=c.pool_rows, max_bs=c.req_to_token.shape[0] - 1,
+                         max_context_len=c.req_to_token.shape[1])
+    runner.req_to_token_pool.req_to_token.copy_(c.req_to_token.to(device))
+    pool = runner.token_to_kv_pool
+    pool.k_buffer[0].copy_(c.k_pool.to(device))
+    pool.v_buffer[0].copy_(c.v_pool.to(device))
+    backend = B200AttnBackend(runner)
+    backend.decode_kernel, backend.extend_kernel = decode_kernel, extend_kernel
+    layer = RadixAttention(num_heads=c.Hq, head_dim=c.D, scaling=c.D**-0.5, num_kv_heads=c.Hkv, layer_id=0)
+    fb = make_forward_batch(c, device)
+    backend.init_forward_metadata(fb)
+    T = c.q.shape[0]
+    out = layer(c.q.to(device).reshape(T, -1), c.k_new.to(device).reshape(T, -1),
+                c.v_new.to(device).reshape(T, -1), fb, backend)
+    torch.cuda.synchronize()
+    return out, pool

@@ -1,0 +1,100 @@
+"""Pins the CPU oracle (oracle/) to outputs of the reference itself (tests/golden/, made by
+oracle/gen_golden.py from /root/reference).  Runs without a GPU."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import DTYPES, GOLDEN, GoldenAttention, from_bits
+from oracle import torch_native_ref as ref
+
+
+@pytest.mark.parametrize("src,dst", [("bf16", "e4m3"), ("bf16", "e5m2"), ("f16", "e4m3"), ("f16", "e5m2")])
+def test_fp8_cast_tables_exhaustive(src, dst):
+    """All 65536 source bit patterns: the C restatement equals torch's cast byte for byte."""
+    z = np.load(GOLDEN / "fp8_cast_tables.npz")
+    sdt = {"bf16": torch.bfloat16, "f16": torch.float16}[src]
+    ddt = {"e4m3": torch.float8_e4m3fn, "e5m2": torch.float8_e5m2}[dst]
+    got = ref.cast_table(sdt, ddt)
+    want = z[f"{src}_to_{dst}"]
+    assert np.array_equal(got, want), f"{int((got != want).sum())} mismatching casts"
+
+
+def test_fp8_cast_documented_edge_values():
+    """SURVEY.md section 9 probe: [1000,448,449,464,465,480,-1000,inf,1e-4,2^-10] -> [nan,448,448,448,448,nan,nan,nan,0,0]."""
+    x = torch.tensor([1000, 448, 449, 464, 465, 480, -1000, float("inf"), 1e-4, 2**-10]).to(torch.bfloat16)
+    table = ref.cast_table(torch.bfloat16, torch.float8_e4m3fn)
+    got = torch.from_numpy(table[x.view(torch.int16).numpy().view(np.uint16)]).view(torch.float8_e4m3fn).float()
+    want = torch.tensor([float("nan"), 448, 448, 448, 448, float("nan"), float("nan"), float("nan"), 0, 0])
+    assert torch.equal(torch.isnan(got), torch.isnan(want))
+    assert torch.equal(got[~torch.isnan(got)], want[~torch.isnan(want)])
+
+
+def _kv_case(z, name):
+    meta = z[f"{name}.meta"]
+    sdt, pdt = DTYPES[int(meta[0])], DTYPES[int(meta[1])]
+    T, H, D, rows = (int(x) for x in meta[2:6])
+    k = from_bits(z[f"{name}.k"], sdt).view(T, H, D)
+    v = from_bits(z[f"{name}.v"], sdt).view(T, H, D)
+    loc = torch.from_numpy(z[f"{name}.loc"].copy())
+    ks, vs = (float(x) for x in z[f"{name}.scales"])
+    return sdt, pdt, T, H, D, rows, k, v, loc, ks, vs
+
+
+def test_store_kv_ref_matches_reference_pool():
+    """C scatter + cast == MHATokenToKVPool.set_kv_buffer on CPU, bit for bit (whole pool)."""
+    z = np.load(GOLDEN / "kv_store.npz")
+    for name in (str(n) for n in z["names"]):
+        sdt, pdt, T, H, D, rows, k, v, loc, ks, vs = _kv_case(z, name)
+        sdtype = torch.uint8 if pdt in (torch.float8_e4m3fn, torch.float8_e5m2) else pdt
+        kc = torch.zeros(rows, H, D, dtype=sdtype)
+        vc = torch.zeros(rows, H, D, dtype=sdtype)
+        ref.store_kv_ref(k, v, kc, vc, loc, cache_dtype=pdt, k_scale=ks, v_scale=vs)
+        want_k = from_bits(z[f"{name}.k_cache"], pdt).view(rows, H, D)
+        want_v = from_bits(z[f"{name}.v_cache"], pdt).view(rows, H, D)
+        assert torch.equal(kc.view(torch.uint8), want_k.view(torch.uint8)), name
+        assert torch.equal(vc.view(torch.uint8), want_v.view(torch.uint8)), name
+
+
+def test_store_kv_ref_skip_and_bounds():
+    k = torch.randn(4, 1, 8).to(torch.bfloat16)
+    kc = torch.zeros(6, 1, 8, dtype=torch.bfloat16)
+    vc = torch.zeros_like(kc)
+    ref.store_kv_ref(k, k, kc, vc, torch.tensor([0, 3, 0, 5]), cache_dtype=torch.bfloat16, skip_index=0)
+    assert torch.equal(kc[0], torch.zeros(1, 8, dtype=torch.bfloat16))  # reserved sink untouched
+    assert torch.equal(kc[3], k[1]) and torch.equal(kc[5], k[3])
+    with pytest.raises(IndexError):
+        ref.store_kv_ref(k, k, kc, vc, torch.tensor([1, 2, 6, 3]), cache_dtype=torch.bfloat16)
+
+
+GA = GoldenAttention()
+
+
+def _oracle_on_case(c):
+    """Oracle run on the golden inputs: store the new rows, then attend."""
+    kc, vc = c.k_pool.clone(), c.v_pool.clone()
+    ref.store_kv_ref(c.k_new, c.v_new, kc, vc, c.out_cache_loc, cache_dtype=c.pool_dtype)
+    seq = torch.tensor(c.seq_lens)
+    if c.is_decode:
+        out = ref.decode_ref(c.q, kc, vc, c.req_to_token, c.req_pool_indices, seq, c.D**-0.5,
+                             kv_dtype=c.pool_dtype)
+    else:
+        out = ref.extend_ref(c.q, kc, vc, c.req_to_token, c.req_pool_indices, torch.tensor(c.prefix_lens),
+                             torch.tensor(c.extend_lens), c.D**-0.5, kv_dtype=c.pool_dtype)
+    return out, kc, vc
+
+
+@pytest.mark.parametrize("name", GA.names)
+def test_attention_oracle_matches_reference(name):
+    c = GA.case(name)
+    out, kc, vc = _oracle_on_case(c)
+    # stored rows: bit-exact against the reference pool
+    loc = c.out_cache_loc
+    assert torch.equal(kc[loc].view(torch.uint8), c.k_rows_after.view(torch.uint8))
+    assert torch.equal(vc[loc].view(torch.uint8), c.v_rows_after.view(torch.uint8))
+    T = c.q.shape[0]
+    # the reference's own code run in float32 on the same pool contents: tight
+    want32 = c.out_ref_fp32.view(T, c.Hq, c.D)
+    assert torch.allclose(out, want32, atol=2e-5, rtol=1e-4), float((out - want32).abs().max())
+    # the reference as it runs in production (model dtype, SDPA internals): dtype-rounding tolerance
+    want = c.out_ref.float().view(T, c.Hq, c.D)
+    assert float((out - want).abs().max()) <= 2e-2
