@@ -1,0 +1,367 @@
+#!/usr/bin/env python
+"""bench.py -- RadixAttention hot-path benchmark on B200 (contract: see DESIGN.md section "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload at N=1 (BASELINE.json configs[1]): Llama-3.1-8B shapes, bf16, TP1, paged decode,
+batch 64 at 4K context, page_size 1, random slot permutation.  One step = one decode step of the
+attention path of all 32 layers: 1 planner launch + 32 x (KV-store scatter, split-KV decode, merge).
+N>1: every rank runs the same per-rank shape on its own KV-head shard (weak scaling, no collective
+inside attention).
+
+One JSON line on stdout (rank 0): metric = decode-attention HBM GB/s (algorithmic bytes / time).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+REPO = Path(__file__).resolve().parent
+if str(REPO) not in sys.path:
+    sys.path.insert(0, str(REPO))
+
+import torch  # noqa: E402
+
+METRIC = "decode_attention_hbm_throughput"
+UNIT = "GB/s"
+
+# Llama-3.1-8B attention shapes
+CFG2 = dict(layers=32, Hq=32, Hkv=8, D=128, bs=64, ctx=4096, page_size=1)
+
+
+def decode_bytes(bs, ctx, Hq, Hkv, D, s_kv=2, layers=1):
+    """Algorithmic bytes of decode attention: KV rows + page table + q/o."""
+    per_layer = bs * ctx * Hkv * 2 * D * s_kv + bs * ctx * 4 + bs * Hq * 2 * D * 2
+    return per_layer * layers
+
+
+def store_bytes(T, Hkv, D, s_kv=2, layers=1):
+    return (T * Hkv * 2 * D * (2 + s_kv) + T * 8) * layers
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--layers", type=int, default=CFG2["layers"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernel", default="auto", choices=["auto", "generic"])
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.lines, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "50",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.perf_counter(), line.strip()))
+
+    def stop(self, t0: float, t1: float):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.proc.terminate()
+        rows = [l.split(", ") for t, l in self.lines if t0 <= t <= t1 + 0.06] or [l.split(", ") for _, l in self.lines]
+        sm, reasons, mx, pw = [], set(), None, []
+        for r in rows:
+            try:
+                sm.append(float(r[0])); mx = float(r[1]); pw.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if val.strip().lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "power_w_max": max(pw) if pw else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+# ----------------------------------------------------------------------------- CPU side (oracle port)
+def cpu_problem(bs, ctx, Hq, Hkv, D, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    rows = bs * ctx + 1
+    kp = torch.randn(rows, Hkv, D, generator=g).to(torch.bfloat16)
+    vp = torch.randn(rows, Hkv, D, generator=g).to(torch.bfloat16)
+    rtt = torch.zeros(bs + 1, ctx, dtype=torch.int32)
+    rtt[1:] = (torch.randperm(rows - 1, generator=g) + 1).view(bs, ctx).to(torch.int32)
+    q = torch.randn(bs, Hq, D, generator=g).to(torch.bfloat16)
+    return q, kp, vp, rtt, torch.arange(1, bs + 1), torch.full((bs,), ctx, dtype=torch.int32)
+
+
+def cpu_decode_throughput(sample_bs, cfg, budget_s, min_reps=1, max_reps=1000):
+    """Times the oracle restatement of the reference's torch_native decode (its CPU path) on all
+    host cores, on `sample_bs` requests x 1 layer of the bench workload.  Returns (GB/s, seconds/rep, reps)."""
+    from oracle import torch_native_ref as ref
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    q, kp, vp, rtt, rpi, seq = cpu_problem(sample_bs, cfg["ctx"], cfg["Hq"], cfg["Hkv"], cfg["D"])
+    scale = cfg["D"] ** -0.5
+    ref.decode_ref(q[:1], kp, vp, rtt, rpi[:1], seq[:1], scale)  # warm-up
+    reps, t0 = 0, time.perf_counter()
+    while reps < min_reps or (time.perf_counter() - t0 < budget_s and reps < max_reps):
+        ref.decode_ref(q, kp, vp, rtt, rpi, seq, scale)
+        reps += 1
+    dt = (time.perf_counter() - t0) / reps
+    gbs = decode_bytes(sample_bs, cfg["ctx"], cfg["Hq"], cfg["Hkv"], cfg["D"]) / dt / 1e9
+    return gbs, dt, reps, cores
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (torch_native semantics; oracle port because the
+    reference tree does not exist on the GPU box) on the host cores, same config/metric/unit.
+    One step = the full batch (64 requests x 4K context) through ONE layer: a bounded sample of the
+    32-layer step, so that K steps finish within minutes."""
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return 0
+    from oracle import torch_native_ref as ref
+
+    cfg = dict(CFG2)
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    q, kp, vp, rtt, rpi, seq = cpu_problem(cfg["bs"], cfg["ctx"], cfg["Hq"], cfg["Hkv"], cfg["D"])
+    scale = cfg["D"] ** -0.5
+    for _ in range(max(args.warmup, 1)):
+        ref.decode_ref(q[:8], kp, vp, rtt, rpi[:8], seq[:8], scale)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ref.decode_ref(q, kp, vp, rtt, rpi, seq, scale)
+    dt = (time.perf_counter() - t0) / args.steps
+    value = decode_bytes(cfg["bs"], cfg["ctx"], cfg["Hq"], cfg["Hkv"], cfg["D"]) / dt / 1e9
+    sample = "1 of 32 layers per step: bs 64 x ctx 4096, Hq 32 / Hkv 8 / D 128, bf16 pool, fp32 math"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt * 1e3, 3), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "llama-3.1-8b decode attention, bs 64 @ 4096 ctx, page_size 1 (BASELINE cfg2)",
+                   "sample": sample},
+        "cpu_baseline": {"value": round(value, 3), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ----------------------------------------------------------------------------- GPU side
+def build_workload(cfg, layers, device, seed):
+    """Mirror pools + backend + per-layer inputs for the decode step (everything resident in HBM)."""
+    sys.path.insert(0, str(REPO / "tests"))
+    from helpers import make_runner
+
+    from sglang_b200.backend import B200AttnBackend
+    from sglang_b200.srt_mirror import ForwardBatch, ForwardMode, RadixAttention
+
+    bs, ctx, Hq, Hkv, D = cfg["bs"], cfg["ctx"], cfg["Hq"], cfg["Hkv"], cfg["D"]
+    rows = bs * ctx + cfg["page_size"]
+    runner = make_runner(device=device, dtype=torch.bfloat16, pool_dtype=torch.bfloat16, Hq=Hq, Hkv=Hkv, D=D,
+                         page_size=cfg["page_size"], pool_rows=rows, max_bs=bs, max_context_len=ctx,
+                         layer_num=layers)
+    g = torch.Generator(device=device).manual_seed(seed)
+    pool, rtp = runner.token_to_kv_pool, runner.req_to_token_pool
+    for l in range(layers):
+        pool.k_buffer[l].normal_(generator=g)
+        pool.v_buffer[l].normal_(generator=g)
+    perm = torch.randperm(rows - 1, generator=g, device=device) + 1
+    rtp.req_to_token[1:].copy_(perm[: bs * ctx].view(bs, ctx).to(torch.int32))
+    backend = B200AttnBackend(runner)
+    layer_objs = [RadixAttention(num_heads=Hq, head_dim=D, scaling=D**-0.5, num_kv_heads=Hkv, layer_id=l)
+                  for l in range(layers)]
+    rpi = torch.arange(1, bs + 1, dtype=torch.int64, device=device)
+    seq = torch.full((bs,), ctx, dtype=torch.int32, device=device)
+    loc = rtp.req_to_token[1:, ctx - 1].to(torch.int64).contiguous()
+    fb = ForwardBatch(forward_mode=ForwardMode.DECODE, batch_size=bs, req_pool_indices=rpi, seq_lens=seq,
+                      out_cache_loc=loc, seq_lens_sum=bs * ctx)
+    width = (Hq + 2 * Hkv) * D
+    qkv = torch.randn(layers, bs, width, generator=g, device=device, dtype=torch.bfloat16)
+    return runner, backend, layer_objs, fb, qkv
+
+
+def split_qkv(qkv_l, cfg):
+    Hq, Hkv, D = cfg["Hq"], cfg["Hkv"], cfg["D"]
+    return qkv_l[:, : Hq * D], qkv_l[:, Hq * D : (Hq + Hkv) * D], qkv_l[:, (Hq + Hkv) * D :]
+
+
+def run_ours(args):
+    rank, world, local = dist_env()
+    import torch.distributed as dist
+
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    from sglang_b200 import ops
+
+    cfg, layers = dict(CFG2), args.layers
+    runner, backend, layer_objs, fb, qkv = build_workload(cfg, layers, device, seed=rank)
+    if args.kernel == "generic":
+        backend.decode_kernel = ops.KERNEL_GENERIC
+    bs, Hq, Hkv, D = cfg["bs"], cfg["Hq"], cfg["Hkv"], cfg["D"]
+
+    def step(events=None):
+        backend.init_forward_metadata(fb)
+        for l in range(layers):
+            q, k, v = split_qkv(qkv[l], cfg)
+            backend.attn_events = events[l] if events is not None else None
+            backend.forward_decode(q, k, v, layer_objs[l], fb)
+        backend.attn_events = None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    # live per-kernel timing: one event pair per (step, layer) around the decode attention kernel
+    pairs = [[(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(layers)]
+             for _ in range(args.steps)]
+    for s_ in pairs:
+        for a, b in s_:
+            a.record(); b.record()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.15)
+    barrier()
+    n0 = ops.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    ev0.record()
+    for s in range(args.steps):
+        step(pairs[s])
+    ev1.record()
+    barrier()
+    t1 = time.perf_counter()
+    launches = ops.launch_count - n0
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    ms = ev0.elapsed_time(ev1) / args.steps
+    kern_ms = sorted(a.elapsed_time(b) for s_ in pairs for a, b in s_)
+    kern_avg = sum(kern_ms) / len(kern_ms)
+
+    # ---- e2e: same step through the backend API with HOST buffers (pinned), copies inside the timed region
+    width = (Hq + 2 * Hkv) * D
+    h_qkv = torch.randn(layers, bs, width).to(torch.bfloat16).pin_memory()
+    h_meta = torch.stack([fb.req_pool_indices.cpu(), fb.seq_lens.cpu().long(), fb.out_cache_loc.cpu()]).pin_memory()
+    h_out = torch.empty(layers, bs, Hq * D, dtype=torch.bfloat16).pin_memory()
+    d_meta = torch.empty_like(h_meta, device=device)
+    from sglang_b200.srt_mirror import ForwardBatch, ForwardMode
+
+    def e2e_step():
+        qkv.copy_(h_qkv, non_blocking=True)
+        d_meta.copy_(h_meta, non_blocking=True)
+        fb2 = ForwardBatch(forward_mode=ForwardMode.DECODE, batch_size=bs, req_pool_indices=d_meta[0],
+                           seq_lens=d_meta[1], out_cache_loc=d_meta[2], seq_lens_sum=bs * cfg["ctx"])
+        backend.init_forward_metadata(fb2)
+        for l in range(layers):
+            q, k, v = split_qkv(qkv[l], cfg)
+            o = backend.forward_decode(q, k, v, layer_objs[l], fb2)
+            h_out[l].copy_(o, non_blocking=True)
+        torch.cuda.current_stream().synchronize()   # the caller reads the result
+
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    e2e_steps = max(args.steps // 2, 5)
+    te0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_ms = (time.perf_counter() - te0) / e2e_steps * 1e3
+    h2d = h_qkv.numel() * 2 + h_meta.numel() * 8
+    d2h = h_out.numel() * 2
+
+    t = torch.tensor([ms, e2e_ms, kern_avg], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms, kern_avg = (float(x) for x in t.cpu())
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    step_bytes = decode_bytes(bs, cfg["ctx"], Hq, Hkv, D, layers=layers) * world
+    value = step_bytes / (ms * 1e-3) / 1e9
+    e2e_value = step_bytes / (e2e_ms * 1e-3) / 1e9
+    peaks = {}
+    pk = REPO / "MEASURED_PEAKS.json"
+    if pk.exists():
+        peaks = json.loads(pk.read_text())
+    peak, peak_src = (float(peaks["hbm_gbs"]), "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    achieved = decode_bytes(bs, cfg["ctx"], Hq, Hkv, D) / (kern_avg * 1e-3) / 1e9
+    traffic = None
+    tf = REPO / "profiles" / "decode_traffic.json"
+    if tf.exists():
+        traffic = json.loads(tf.read_text()).get("dram_bytes_per_launch")
+    line = {
+        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "llama-3.1-8b decode attention, bs 64 @ 4096 ctx, page_size 1 (BASELINE cfg2)",
+                   "layers": layers, "heads_per_gpu": [Hq, Hkv], "head_dim": D, "parallelism": f"tp{world}-head-shards",
+                   "l2": "inputs larger than L2 (1.07 GB of KV per layer vs 126 MB L2); no flush",
+                   "decode_kernel": args.kernel},
+        "tokens_per_s": round(bs * world / (ms * 1e-3), 1),
+        "pct_of_8TBs": round(100 * value / world / 8000.0, 2),
+        "roofline": {"bound": "hbm", "kernel": "decode_mma_kernel", "achieved": round(achieved, 1), "peak": peak,
+                     "peak_source": peak_src, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                     "frac_of_8TBs_nominal": round(achieved / 8000.0, 4), "kernel_us_avg": round(kern_avg * 1e3, 2),
+                     "kernel_us_median": round(kern_ms[len(kern_ms) // 2] * 1e3, 2), "traffic": traffic},
+        "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "ms_per_step": round(e2e_ms, 4),
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches,
+        "clocks": clocks,
+    }
+    if not args.no_cpu_baseline:
+        gbs, dt, reps, cores = cpu_decode_throughput(8, cfg, budget_s=12.0)
+        line["cpu_baseline"] = {"value": round(gbs, 3), "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"8 of 64 requests x 1 of {layers} layers at ctx 4096, {reps} reps, "
+                                          f"{dt:.3f} s each (oracle/torch_native_ref.decode_ref, fp32)"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -159,6 +159,8 @@ typedef struct b200_decode_args {
   float* ws_lse;             /* [max_chunks * Hq] partial log2-sum-exp */
   int32_t num_ctas;          /* persistent grid size (same as in the plan) */
   int32_t kernel;            /* B200_KERNEL_* */
+  void* ev_attn_start;       /* optional cudaEvent_t recorded right before the attention kernel */
+  void* ev_attn_stop;        /* optional cudaEvent_t recorded right after it (before the merge) */
 } b200_decode_args;
 
 int b200attn_decode(const b200_decode_args* args, b200_stream_t stream);

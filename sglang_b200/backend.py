@@ -82,6 +82,8 @@ class B200AttnBackend(_Base):
         self.extend_ws: Optional[ops.ExtendWorkspace] = None
         self._extend_block_q = 64
         self.forward_metadata = None
+        #: optional (start, stop) torch.cuda.Event pair re-recorded around the next decode attention kernel
+        self.attn_events = None
 
     # ------------------------------------------------------------------ metadata
     def init_forward_metadata_out_graph(self, forward_batch, in_capture: bool = False):
@@ -193,6 +195,7 @@ class B200AttnBackend(_Base):
             self.decode_ws, layer.scaling,
             kv_dtype=self.kv_dtype, k_scale=k_descale, v_scale=v_descale,
             logit_cap=float(getattr(layer, "logit_cap", 0.0) or 0.0), kernel=self.decode_kernel,
+            attn_events=self.attn_events,
         )
         return o
 

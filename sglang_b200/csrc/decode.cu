@@ -378,6 +378,7 @@ extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_)
                  a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype);
   const bool use_fast = fast_ok && a->kernel != B200_KERNEL_GENERIC && a->logit_cap == 0.f;
   int rc;
+  if (a->ev_attn_start) B200_CHECK_CUDA(cudaEventRecord(reinterpret_cast<cudaEvent_t>(a->ev_attn_start), stream));
   if (use_fast) {
     rc = launch_decode_fast(p, a->q_dtype, a->kv_dtype, a->num_ctas, stream);
   } else if (a->q_dtype == B200_BF16) {
@@ -386,6 +387,7 @@ extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_)
     rc = launch_generic<__half>(p, a->kv_dtype, a->num_ctas, stream);
   }
   if (rc != B200_OK) return rc;
+  if (a->ev_attn_stop) B200_CHECK_CUDA(cudaEventRecord(reinterpret_cast<cudaEvent_t>(a->ev_attn_stop), stream));
   const int64_t rows = (int64_t)a->batch_size * a->num_q_heads;
   const unsigned mgrid = (unsigned)((rows + kMergeWarps - 1) / kMergeWarps);
   if (a->q_dtype == B200_BF16) {

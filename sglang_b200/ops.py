@@ -176,7 +176,11 @@ def decode_attention(
     v_scale: float = 1.0,
     logit_cap: float = 0.0,
     kernel: int = KERNEL_AUTO,
+    attn_events=None,
 ) -> torch.Tensor:
+    """`attn_events`: optional (start, stop) torch.cuda.Event pair (already recorded once, so the
+    handles exist) that the library re-records around the attention kernel alone -- bench.py's
+    live per-kernel timing."""
     global launch_count
     _need_cuda(q, o, k_cache, v_cache, req_to_token, req_pool_indices, seq_lens)
     if q.dim() != 3 or o.dim() != 3 or k_cache.dim() != 3 or v_cache.dim() != 3:
@@ -202,6 +206,8 @@ def decode_attention(
         sm_scale=float(sm_scale), k_scale=float(k_scale), v_scale=float(v_scale), logit_cap=float(logit_cap),
         plan=ws.plan.data_ptr(), max_bs=ws.max_bs, max_chunks=ws.max_chunks,
         ws_o=ws.ws_o.data_ptr(), ws_lse=ws.ws_lse.data_ptr(), num_ctas=ws.num_ctas, kernel=kernel,
+        ev_attn_start=attn_events[0].cuda_event if attn_events else None,
+        ev_attn_stop=attn_events[1].cuda_event if attn_events else None,
     )
     if ws.ws_o.numel() < ws.max_chunks * Hq * Dv or ws.ws_lse.numel() < ws.max_chunks * Hq:
         raise ValueError("decode workspace too small for this head configuration")

@@ -1,0 +1,122 @@
+"""GPU parity: paged decode attention through B200AttnBackend / the C ABI.
+Tolerance is BASELINE.json's: max-abs <= 2e-2 against the FP32-accumulated oracle."""
+import pytest
+import torch
+
+from helpers import ATOL, GoldenAttention, run_backend_on_case, store_dtype
+from oracle import torch_native_ref as ref
+
+pytestmark = pytest.mark.gpu
+
+GA = GoldenAttention()
+DECODE_CASES = [n for n in GA.names if GA.case(n).is_decode]
+KERNELS = {"generic": 1, "auto": 0}
+
+
+@pytest.mark.parametrize("kernel", list(KERNELS))
+@pytest.mark.parametrize("name", DECODE_CASES)
+def test_golden_decode(name, kernel):
+    """Reference kit cases (12 x 3 slot layouts) + scaled BASELINE configs, run by the reference on CPU."""
+    c = GA.case(name)
+    out, pool = run_backend_on_case(c, decode_kernel=KERNELS[kernel])
+    T = c.q.shape[0]
+    got = out.float().cpu().view(T, c.Hq, c.D)
+    err = float((got - c.out_ref_fp32.view(T, c.Hq, c.D)).abs().max())
+    assert err <= ATOL, f"{name}: max-abs {err}"
+    # the rows this step stored: bit-exact against the reference pool
+    loc = c.out_cache_loc
+    assert torch.equal(pool.k_buffer[0][loc.cuda()].cpu().view(torch.uint8), c.k_rows_after.view(torch.uint8))
+    assert torch.equal(pool.v_buffer[0][loc.cuda()].cpu().view(torch.uint8), c.v_rows_after.view(torch.uint8))
+
+
+def _random_problem(bs, Hq, Hkv, D, lens, page_size, dtype, pool_dtype, seed, idx_dtype=torch.int64):
+    g = torch.Generator().manual_seed(seed)
+    n_pages = sum((L + page_size - 1) // page_size for L in lens) + 3
+    rows = (n_pages + 1) * page_size
+    perm = (torch.randperm(n_pages, generator=g) + 1).tolist()
+    max_ctx = max(lens) + 1
+    rtt = torch.zeros(bs + 1, max_ctx, dtype=torch.int32)
+    for r, L in enumerate(lens):
+        pos = 0
+        while pos < L:
+            pg = perm.pop()
+            n = min(page_size, L - pos)
+            rtt[r + 1, pos : pos + n] = torch.arange(pg * page_size, pg * page_size + n)
+            pos += n
+    q = torch.randn(bs, Hq, D, generator=g).to(dtype)
+    kp = torch.randn(rows, Hkv, D, generator=g).to(dtype)
+    vp = torch.randn(rows, Hkv, D, generator=g).to(dtype)
+    if store_dtype(pool_dtype) == torch.uint8:
+        kp, vp = kp.to(pool_dtype).view(torch.uint8), vp.to(pool_dtype).view(torch.uint8)
+    return q, kp, vp, rtt, torch.arange(1, bs + 1, dtype=idx_dtype), torch.tensor(lens, dtype=torch.int32)
+
+
+def _run_ops_decode(q, kp, vp, rtt, rpi, seq, scale, pool_dtype, kernel=0, fixed_chunk=0, k_scale=1.0, v_scale=1.0,
+                    logit_cap=0.0):
+    from sglang_b200 import ops
+
+    sm, _, _ = ops.device_info()
+    bs, Hq, D = q.shape
+    ws = ops.DecodeWorkspace.create(bs, Hq, D, "cuda", num_ctas=sm * 2)
+    seq_g = seq.cuda()
+    ops.decode_plan(ws, seq_g, kp.shape[1], fixed_chunk_tokens=fixed_chunk)
+    o = torch.empty_like(q, device="cuda")
+    ops.decode_attention(q.cuda(), o, kp.cuda(), vp.cuda(), rtt.cuda(), rpi.cuda(), seq_g, ws, scale,
+                         kv_dtype=pool_dtype, k_scale=k_scale, v_scale=v_scale, logit_cap=logit_cap, kernel=kernel)
+    torch.cuda.synchronize()
+    return o.float().cpu(), ws
+
+
+SHAPES = [
+    # bs, Hq, Hkv, D, lens, page
+    (3, 32, 8, 128, [1, 17, 600], 1),          # Llama-8B heads, ragged incl. length 1
+    (5, 8, 1, 128, [2048, 33, 700, 64, 65], 16),  # 70B TP8 shard
+    (2, 14, 2, 64, [515, 575], 1),             # Qwen2.5-0.5B heads (group 7)
+    (2, 16, 1, 128, [300, 129], 1),            # group 16 (upper MMA rows)
+    (2, 4, 4, 256, [90, 257], 32),             # MHA, D 256
+    (2, 4, 4, 80, [70, 33], 1),                # odd head dims -> generic path
+    (2, 4, 2, 13, [40, 9], 1),
+    (1, 64, 2, 64, [130], 1),                  # group 32 -> generic path
+]
+
+
+@pytest.mark.parametrize("kernel", list(KERNELS))
+@pytest.mark.parametrize("dtype,pool_dtype", [(torch.bfloat16, torch.bfloat16), (torch.float16, torch.float16),
+                                              (torch.bfloat16, torch.float8_e4m3fn)])
+@pytest.mark.parametrize("shape", SHAPES, ids=[f"bs{s[0]}_h{s[1]}_{s[2]}_d{s[3]}_p{s[5]}" for s in SHAPES])
+def test_decode_vs_oracle(shape, dtype, pool_dtype, kernel):
+    """Configs follow the reference's Triton kernel test (B,Hq,Hkv,D) grid, test_triton_attention_kernels.py:563-573."""
+    bs, Hq, Hkv, D, lens, page = shape
+    q, kp, vp, rtt, rpi, seq = _random_problem(bs, Hq, Hkv, D, lens, page, dtype, pool_dtype, seed=D + bs)
+    scale = D**-0.5
+    got, _ = _run_ops_decode(q, kp, vp, rtt, rpi, seq, scale, pool_dtype, kernel=KERNELS[kernel])
+    want = ref.decode_ref(q, kp, vp, rtt, rpi, seq, scale, kv_dtype=pool_dtype)
+    err = float((got - want).abs().max())
+    assert err <= ATOL, f"max-abs {err}"
+
+
+def test_decode_fp8_descale_and_logit_cap():
+    q, kp, vp, rtt, rpi, seq = _random_problem(3, 8, 2, 128, [400, 3, 129], 1, torch.bfloat16,
+                                               torch.float8_e4m3fn, seed=11)
+    scale = 128**-0.5
+    got, _ = _run_ops_decode(q, kp, vp, rtt, rpi, seq, scale, torch.float8_e4m3fn, k_scale=0.5, v_scale=1.75)
+    want = ref.decode_ref(q, kp, vp, rtt, rpi, seq, scale, kv_dtype=torch.float8_e4m3fn, k_scale=0.5, v_scale=1.75)
+    assert float((got - want).abs().max()) <= ATOL
+    got, _ = _run_ops_decode(q, kp, vp, rtt, rpi, seq, scale, torch.float8_e4m3fn, logit_cap=5.0)
+    want = ref.decode_ref(q, kp, vp, rtt, rpi, seq, scale, kv_dtype=torch.float8_e4m3fn, logit_cap=5.0)
+    assert float((got - want).abs().max()) <= ATOL
+
+
+@pytest.mark.parametrize("idx_dtype", [torch.int32, torch.int64])
+def test_split_invariance_and_index_dtypes(idx_dtype):
+    """The split-KV result must not depend on how the planner cuts the sequence (64-token vs one chunk)."""
+    q, kp, vp, rtt, rpi, seq = _random_problem(4, 32, 8, 128, [1000, 64, 63, 2500], 1, torch.bfloat16,
+                                               torch.bfloat16, seed=3, idx_dtype=idx_dtype)
+    scale = 128**-0.5
+    a, ws_a = _run_ops_decode(q, kp, vp, rtt, rpi, seq, scale, torch.bfloat16, fixed_chunk=64)
+    b, ws_b = _run_ops_decode(q, kp, vp, rtt, rpi, seq, scale, torch.bfloat16, fixed_chunk=4096)
+    assert int(ws_a.plan[0]) == 64 and int(ws_b.plan[0]) == 4096
+    assert int(ws_a.plan[1]) == sum((L + 63) // 64 for L in [1000, 64, 63, 2500]) and int(ws_b.plan[1]) == 4
+    assert float((a - b).abs().max()) <= 4e-3
+    want = ref.decode_ref(q, kp, vp, rtt, rpi, seq, scale)
+    assert float((a - want).abs().max()) <= ATOL
