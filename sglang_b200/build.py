@@ -63,7 +63,7 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path:
         if proc.returncode != 0:
             raise RuntimeError(f"nvcc failed on {src}:\n{out}")
     (LIB_DIR / "ptxas.log").write_text("\n".join(log))
-    cmd = [nvcc, "-shared", "-o", str(LIB_PATH), *map(str, objs)]
+    cmd = [nvcc, "-shared", "-Wno-deprecated-gpu-targets", "-o", str(LIB_PATH), *map(str, objs)]
     subprocess.run(cmd, check=True)
     if verbose:
         print(f"built {LIB_PATH}")

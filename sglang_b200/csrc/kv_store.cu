@@ -34,10 +34,6 @@ struct StoreParams {
   int32_t loc_is_i64;
 };
 
-template <typename T> struct Vec8;             // 8 elements of T as one vector register group
-template <> struct Vec8<__nv_bfloat16> { uint4 raw; };
-template <> struct Vec8<__half> { uint4 raw; };
-
 __device__ __forceinline__ uint4 ld_stream_16(const void* p) {
   uint4 r;
   asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -59,6 +55,8 @@ template <> __device__ __forceinline__ float src_bits_to_float<__nv_bfloat16>(ui
   return __uint_as_float((uint32_t)b << 16);
 }
 template <> __device__ __forceinline__ float src_bits_to_float<__half>(uint16_t b) {
+  // cvt.f32.f16 canonicalises NaNs (drops the sign); torch keeps it, and the FP8 cast copies it
+  if ((b & 0x7fffu) > 0x7c00u) return __uint_as_float(((uint32_t)(b & 0x8000u) << 16) | 0x7fc00000u);
   return __half2float(__ushort_as_half(b));
 }
 template <typename SRC> __device__ __forceinline__ float round_to_src(float f);
