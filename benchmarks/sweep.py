@@ -1,0 +1,167 @@
+#!/usr/bin/env python
+"""Kernel-level sweep over BASELINE.json's configs (one layer each), CUDA-event timed.
+
+    python benchmarks/sweep.py [--only decode|extend|store] [--iters 30] [--json out.json]
+
+Prints one line per case: kernel time, achieved GB/s (decode/store) or TFLOP/s (extend) and the
+fraction of the measured / nominal B200 peaks.  Not the contract benchmark (that is bench.py);
+this is the table DESIGN.md and profiles/ quote for cfg3-cfg5.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import sys
+from pathlib import Path
+
+import torch
+
+REPO = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(REPO))
+from sglang_b200 import ops  # noqa: E402
+
+PEAKS = json.loads((REPO / "MEASURED_PEAKS.json").read_text()) if (REPO / "MEASURED_PEAKS.json").exists() else {}
+HBM = float(PEAKS.get("hbm_gbs", 6650.0))
+TF = float(PEAKS.get("bf16_tflops", 1590.0))
+
+
+def time_cuda(fn, iters, warmup=5):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
+    for a, b in evs:
+        a.record(); fn(); b.record()
+    torch.cuda.synchronize()
+    ts = sorted(a.elapsed_time(b) for a, b in evs)
+    return ts[len(ts) // 2] * 1e-3
+
+
+def decode_case(name, bs, L, Hq, Hkv, D, pool_dtype, page, iters, ragged=False):
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(0)
+    lens = torch.full((bs,), L, dtype=torch.int32, device=dev)
+    if ragged:
+        lens = torch.randint(L // 2, L + 1, (bs,), generator=g, device=dev, dtype=torch.int32)
+    n_pages = bs * ((L + page - 1) // page)
+    rows = (n_pages + 1) * page
+    es = 1 if pool_dtype == torch.float8_e4m3fn else 2
+    kp = torch.randn(rows, Hkv, D, generator=g, device=dev, dtype=torch.bfloat16)
+    vp = torch.randn(rows, Hkv, D, generator=g, device=dev, dtype=torch.bfloat16)
+    if es == 1:
+        kp, vp = kp.to(pool_dtype).view(torch.uint8), vp.to(pool_dtype).view(torch.uint8)
+    perm = torch.randperm(n_pages, generator=g, device=dev) + 1
+    ppr = (L + page - 1) // page
+    rtt = torch.zeros(bs + 1, ppr * page, dtype=torch.int32, device=dev)
+    rtt[1:] = (perm.view(bs, ppr, 1) * page + torch.arange(page, device=dev).view(1, 1, page)).view(bs, -1).int()
+    q = torch.randn(bs, Hq, D, generator=g, device=dev, dtype=torch.bfloat16)
+    o = torch.empty_like(q)
+    rpi = torch.arange(1, bs + 1, device=dev)
+    sm, _, _ = ops.device_info()
+    ws = ops.DecodeWorkspace.create(bs, Hq, D, dev, num_ctas=sm * ops.decode_ctas_per_sm(D, pool_dtype))
+    ops.decode_plan(ws, lens, Hkv)
+
+    def fn():
+        ops.decode_attention(q, o, kp, vp, rtt, rpi, lens, ws, D**-0.5, kv_dtype=pool_dtype)
+
+    t = time_cuda(fn, iters)
+    tot = int(lens.sum())
+    nbytes = tot * Hkv * 2 * D * es + tot * 4 + bs * Hq * 2 * D * 2
+    gbs = nbytes / t / 1e9
+    return dict(case=name, kind="decode", us=round(t * 1e6, 1), gbs=round(gbs, 1), frac_measured=round(gbs / HBM, 3),
+                frac_8tbs=round(gbs / 8000, 3), chunk=int(ws.plan[0]), chunks=int(ws.plan[1]))
+
+
+def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0):
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(0)
+    rows = (P if shared else bs * P) + bs * E + 1
+    kp = torch.randn(rows, Hkv, D, generator=g, device=dev, dtype=torch.bfloat16)
+    vp = torch.randn(rows, Hkv, D, generator=g, device=dev, dtype=torch.bfloat16)
+    perm = torch.randperm(rows - 1, generator=g, device=dev).int() + 1
+    rtt = torch.zeros(bs + 1, P + E, dtype=torch.int32, device=dev)
+    if shared:
+        rtt[1:, :P] = perm[:P]
+        rtt[1:, P:] = perm[P : P + bs * E].view(bs, E)
+    else:
+        rtt[1:] = perm[: bs * (P + E)].view(bs, P + E)
+    T = bs * E
+    q = torch.randn(T, Hq, D, generator=g, device=dev, dtype=torch.bfloat16)
+    o = torch.empty_like(q)
+    rpi = torch.arange(1, bs + 1, device=dev)
+    pre = torch.full((bs,), P, dtype=torch.int32, device=dev)
+    ext = torch.full((bs,), E, dtype=torch.int32, device=dev)
+    sm, _, _ = ops.device_info()
+    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, torch.bfloat16, kernel)
+    ws = ops.ExtendWorkspace.create(bs, T // bq + bs + 1, dev, num_ctas=sm)
+    ops.extend_plan(ws, ext, bq)
+
+    def fn():
+        ops.extend_attention(q, o, kp, vp, rtt, rpi, pre, ext, ws, D**-0.5, kernel=kernel)
+
+    t = time_cuda(fn, iters, warmup=2)
+    flops = 4 * Hq * D * bs * (E * P + E * (E + 1) / 2)
+    tf = flops / t / 1e12
+    return dict(case=name, kind="extend", ms=round(t * 1e3, 3), tflops=round(tf, 1), frac_measured=round(tf / TF, 3),
+                frac_nominal=round(tf / 2250, 3))
+
+
+def store_case(name, T, Hkv, D, pool_dtype, iters):
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(0)
+    rows = max(T * 2, 1 << 18) + 1
+    k = torch.randn(T, Hkv, D, generator=g, device=dev, dtype=torch.bfloat16)
+    v = torch.randn(T, Hkv, D, generator=g, device=dev, dtype=torch.bfloat16)
+    es = 1 if pool_dtype == torch.float8_e4m3fn else 2
+    kc = torch.zeros(rows, Hkv, D, device=dev, dtype=torch.uint8 if es == 1 else torch.bfloat16)
+    vc = torch.zeros_like(kc)
+    loc = torch.randperm(rows - 1, generator=g, device=dev)[:T] + 1
+    t = time_cuda(lambda: ops.store_kv(k, v, kc, vc, loc, cache_dtype=pool_dtype), iters)
+    nbytes = T * Hkv * 2 * D * (2 + es) + T * 8
+    gbs = nbytes / t / 1e9
+    return dict(case=name, kind="store", us=round(t * 1e6, 2), gbs=round(gbs, 1), frac_measured=round(gbs / HBM, 3))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--only", default="")
+    ap.add_argument("--iters", type=int, default=30)
+    ap.add_argument("--json", default="")
+    ap.add_argument("--quick", action="store_true")
+    a = ap.parse_args()
+    bf, e4 = torch.bfloat16, torch.float8_e4m3fn
+    out = []
+
+    def emit(r):
+        out.append(r)
+        print(json.dumps(r), flush=True)
+
+    if a.only in ("", "decode"):
+        emit(decode_case("cfg2 8B bf16 bs64 ctx4096 page1", 64, 4096, 32, 8, 128, bf, 1, a.iters))
+        emit(decode_case("cfg2 8B bf16 bs64 ctx4096 page16", 64, 4096, 32, 8, 128, bf, 16, a.iters))
+        emit(decode_case("cfg2 ragged U[2048,4096]", 64, 4096, 32, 8, 128, bf, 1, a.iters, ragged=True))
+        emit(decode_case("cfg3 8B fp8 bs256 ctx8192", 256, 8192, 32, 8, 128, e4, 1, a.iters))
+        for tp, (hq, hkv) in ((2, (32, 4)), (4, (16, 2)), (8, (8, 1))):
+            for bs in (8, 32):
+                emit(decode_case(f"cfg4 70B tp{tp} bs{bs} ctx32768", bs, 32768, hq, hkv, 128, bf, 1, a.iters))
+        emit(decode_case("cfg4 70B tp8 fp8 bs32 ctx32768", 32, 32768, 8, 1, 128, e4, 1, a.iters))
+        emit(decode_case("small bs1 ctx4096 8B", 1, 4096, 32, 8, 128, bf, 1, a.iters))
+    if a.only in ("", "store"):
+        emit(store_case("decode store 64 rows 8B bf16", 64, 8, 128, bf, a.iters))
+        emit(store_case("decode store 256 rows 8B fp8", 256, 8, 128, e4, a.iters))
+        emit(store_case("cfg5 store 131072 rows 8B bf16", 131072, 8, 128, bf, a.iters))
+        emit(store_case("cfg5 store 131072 rows 8B fp8", 131072, 8, 128, e4, a.iters))
+    if a.only in ("", "extend"):
+        it = max(3, a.iters // 10)
+        emit(extend_case("cfg5/16 8 req x (16K shared prefix + 1K)", 8, 16384, 1024, 32, 8, 128, it))
+        if not a.quick:
+            emit(extend_case("cfg5 128 req x (16K shared prefix + 1K)", 128, 16384, 1024, 32, 8, 128, it))
+            emit(extend_case("cfg5 no sharing 16 req x (16K + 1K)", 16, 16384, 1024, 32, 8, 128, it, shared=False))
+        emit(extend_case("prefill 8 req x 4K no prefix", 8, 0, 4096, 32, 8, 128, it))
+        emit(extend_case("70B tp8 4 req x (8K + 2K)", 4, 8192, 2048, 8, 1, 128, it))
+    if a.json:
+        Path(a.json).write_text(json.dumps(out, indent=1))
+
+
+if __name__ == "__main__":
+    main()

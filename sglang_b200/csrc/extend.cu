@@ -13,6 +13,7 @@
 
 #include "common.cuh"
 #include "generic_attn.cuh"
+#include "sm100_ptx.cuh"
 
 namespace b200 {
 namespace {
