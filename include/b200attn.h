@@ -118,8 +118,8 @@ typedef struct b200_decode_plan_args {
   int32_t max_chunks;
   int32_t num_kv_heads;      /* work multiplicity per chunk */
   int32_t num_ctas;          /* persistent CTAs the decode kernel will run */
-  int32_t waves;             /* target work items per CTA (load-balance granularity) */
-  int32_t min_chunk_tokens;  /* multiple of 64 */
+  int32_t waves;             /* most work items per CTA (load-balance granularity) */
+  int32_t min_chunk_tokens;  /* preferred smallest chunk (tokens x kv heads per item), multiple of 64 */
   int32_t fixed_chunk_tokens;/* > 0 overrides the heuristic (deterministic splits) */
   int32_t* plan;             /* device, b200attn_decode_plan_ints() ints */
 } b200_decode_plan_args;
@@ -157,6 +157,7 @@ typedef struct b200_decode_args {
   int32_t max_bs, max_chunks;
   float* ws_o;               /* [max_chunks * Hq * Dv] partial outputs */
   float* ws_lse;             /* [max_chunks * Hq] partial log2-sum-exp */
+  int32_t* ws_counters;      /* [max_bs * Hkv] zero-initialised once; the fused merge leaves them zero */
   int32_t num_ctas;          /* persistent grid size (same as in the plan) */
   int32_t kernel;            /* B200_KERNEL_* */
   void* ev_attn_start;       /* optional cudaEvent_t recorded right before the attention kernel */

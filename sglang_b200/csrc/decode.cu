@@ -68,9 +68,16 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanPar
     if (p.fixed_chunk > 0) {
       chunk = p.fixed_chunk;
     } else {
-      const int64_t target = (int64_t)p.num_ctas * p.waves;
-      chunk = (total * p.num_kv_heads + target - 1) / (target > 0 ? target : 1);
-      if (chunk < p.min_chunk) chunk = p.min_chunk;
+      // tokens x kv-heads each persistent CTA has to stream
+      const int64_t per_cta = (total * p.num_kv_heads + p.num_ctas - 1) / p.num_ctas;
+      if (per_cta <= p.min_chunk) {
+        chunk = per_cta;                 // small problem: about one work item per CTA
+      } else {
+        int64_t w = per_cta / p.min_chunk;   // large problem: up to `waves` items per CTA, each >= min_chunk
+        if (w > p.waves) w = p.waves;
+        chunk = (per_cta + w - 1) / w;
+      }
+      if (chunk < 64) chunk = 64;
     }
     chunk = (chunk + 63) / 64 * 64;
     // capacity: sum_r ceil(L_r / chunk) <= total / chunk + bs must fit the work list
@@ -152,6 +159,7 @@ struct DecodeParams {
   const int32_t* plan;
   float* ws_o;
   float* ws_lse;
+  int32_t* ws_cnt;   // [bs * Hkv] arrival counters of the fused split merge (self-resetting)
   int64_t q_stride_t, q_stride_h, o_stride_t, o_stride_h;
   int64_t k_stride_s, k_stride_h, v_stride_s, v_stride_h;
   int64_t req_to_token_stride;
@@ -178,10 +186,13 @@ __device__ __forceinline__ ChunkInfo load_chunk(const DecodeParams& p, int c) {
   ci.req = chunk_req[c];
   const int off = chunk_offset[ci.req];
   ci.n_chunks = chunk_offset[ci.req + 1] - off;
-  ci.start = (c - off) * chunk;
   const int64_t L = load_index(p.seq_lens, p.seq_lens_is_i64, ci.req);
+  // equal-sized chunks inside a request: n = ceil(L / chunk) pieces of roundup64(ceil(L / n)) tokens
+  const int cs = (int)(((L + ci.n_chunks - 1) / ci.n_chunks + 63) / 64 * 64);
+  ci.start = (c - off) * cs;
   const int64_t rem = L - ci.start;
-  ci.n_tok = (int)(rem < chunk ? rem : chunk);
+  ci.n_tok = (int)(rem < cs ? rem : cs);
+  (void)chunk;
   ci.pool_row = load_index(p.req_pool_indices, p.req_pool_indices_is_i64, ci.req);
   return ci;
 }
@@ -344,7 +355,7 @@ extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_)
   B200_CHECK_ARG(a != nullptr, "decode: null args");
   if (a->batch_size == 0) return B200_OK;
   B200_CHECK_ARG(a->q && a->o && a->k_cache && a->v_cache && a->req_to_token && a->req_pool_indices &&
-                     a->seq_lens && a->plan && a->ws_o && a->ws_lse,
+                     a->seq_lens && a->plan && a->ws_o && a->ws_lse && a->ws_counters,
                  "decode: null pointer");
   B200_CHECK_ARG(a->num_q_heads > 0 && a->num_kv_heads > 0 && a->num_q_heads % a->num_kv_heads == 0,
                  "decode: Hq=%d must be a multiple of Hkv=%d", a->num_q_heads, a->num_kv_heads);
@@ -359,7 +370,7 @@ extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_)
   DecodeParams p;
   p.q = a->q; p.o = a->o; p.k_cache = a->k_cache; p.v_cache = a->v_cache;
   p.req_to_token = a->req_to_token; p.req_pool_indices = a->req_pool_indices; p.seq_lens = a->seq_lens;
-  p.plan = a->plan; p.ws_o = a->ws_o; p.ws_lse = a->ws_lse;
+  p.plan = a->plan; p.ws_o = a->ws_o; p.ws_lse = a->ws_lse; p.ws_cnt = a->ws_counters;
   p.q_stride_t = a->q_stride_t; p.q_stride_h = a->q_stride_h;
   p.o_stride_t = a->o_stride_t; p.o_stride_h = a->o_stride_h;
   p.k_stride_s = a->k_stride_s; p.k_stride_h = a->k_stride_h;
@@ -388,6 +399,7 @@ extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_)
   }
   if (rc != B200_OK) return rc;
   if (a->ev_attn_stop) B200_CHECK_CUDA(cudaEventRecord(reinterpret_cast<cudaEvent_t>(a->ev_attn_stop), stream));
+  if (use_fast) return B200_OK;   // the fast kernel merges its splits itself (last-arriving CTA)
   const int64_t rows = (int64_t)a->batch_size * a->num_q_heads;
   const unsigned mgrid = (unsigned)((rows + kMergeWarps - 1) / kMergeWarps);
   if (a->q_dtype == B200_BF16) {

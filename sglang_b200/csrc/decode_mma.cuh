@@ -336,33 +336,79 @@ __global__ void __launch_bounds__(kFastWarps* kWarp, (FastCfg<D, KV>::kCtaSmem >
       if constexpr (UPPER) { ml_s[8 + qrow] = m_run[1]; ml_s[16 + 8 + qrow] = l_run[1]; }
     }
     __syncthreads();
-    {
-      const bool final_out = ci.n_chunks == 1;
-      for (int idx = threadIdx.x; idx < g * D; idx += kFastWarps * kWarp) {
-        const int row = idx / D, d = idx - row * D;
-        float mw[kFastWarps], M = -INFINITY;
+    const bool final_out = ci.n_chunks == 1;
+    for (int idx = threadIdx.x; idx < g * D; idx += kFastWarps * kWarp) {
+      const int row = idx / D, d = idx - row * D;
+      float mw[kFastWarps], M = -INFINITY;
 #pragma unroll
-        for (int w = 0; w < kFastWarps; ++w) {
-          mw[w] = reinterpret_cast<const float*>(smem + w * C::kWarpSmem)[16 * D + row];
-          M = fmaxf(M, mw[w]);
-        }
-        float num = 0.f, den = 0.f;
+      for (int w = 0; w < kFastWarps; ++w) {
+        mw[w] = reinterpret_cast<const float*>(smem + w * C::kWarpSmem)[16 * D + row];
+        M = fmaxf(M, mw[w]);
+      }
+      float num = 0.f, den = 0.f;
 #pragma unroll
-        for (int w = 0; w < kFastWarps; ++w) {
-          const float* ow = reinterpret_cast<const float*>(smem + w * C::kWarpSmem);
-          const float wgt = fast_exp2(mw[w] - M);
-          num = fmaf(wgt, ow[row * D + d], num);
-          den = fmaf(wgt, ow[16 * D + 16 + row], den);
+      for (int w = 0; w < kFastWarps; ++w) {
+        const float* ow = reinterpret_cast<const float*>(smem + w * C::kWarpSmem);
+        const float wgt = fast_exp2(mw[w] - M);
+        num = fmaf(wgt, ow[row * D + d], num);
+        den = fmaf(wgt, ow[16 * D + 16 + row], den);
+      }
+      const int h = kvh * g + row;
+      const float val = num / den;
+      if (final_out) {
+        reinterpret_cast<QT*>(p.o)[(int64_t)ci.req * p.o_stride_t + (int64_t)h * p.o_stride_h + d] =
+            from_float<QT>(val * p.v_scale);
+      } else {
+        p.ws_o[((int64_t)c * Hq + h) * D + d] = val;
+        if (d == 0) p.ws_lse[(int64_t)c * Hq + h] = M + log2f(den);
+      }
+    }
+    // ---- fused split merge: the CTA that publishes the last partial of (request, kv head) combines them ----
+    if (!final_out) {
+      __shared__ int s_last;
+      __threadfence();                       // partials visible device-wide before the arrival count
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        const int prev = atomicAdd(p.ws_cnt + ci.req * Hkv + kvh, 1);
+        s_last = prev == ci.n_chunks - 1;
+      }
+      __syncthreads();
+      if (s_last) {
+        __threadfence();
+        const int c0 = p.plan[kPlanHeader + ci.req];   // first chunk of this request
+        float* s_m = reinterpret_cast<float*>(smem);   // [16] row max, [16] 1/denominator
+        for (int row = warp; row < g; row += kFastWarps) {
+          const int h = kvh * g + row;
+          float mx = -INFINITY;
+          for (int i = lane; i < ci.n_chunks; i += kWarp) mx = fmaxf(mx, __ldcg(p.ws_lse + (int64_t)(c0 + i) * Hq + h));
+          mx = warp_max(mx);
+          float dn = 0.f;
+          for (int i = lane; i < ci.n_chunks; i += kWarp)
+            dn += fast_exp2(__ldcg(p.ws_lse + (int64_t)(c0 + i) * Hq + h) - mx);
+          dn = warp_sum(dn);
+          if (lane == 0) { s_m[row] = mx; s_m[16 + row] = p.v_scale / dn; }
         }
-        const int h = kvh * g + row;
-        const float val = num / den;
-        if (final_out) {
+        __syncthreads();
+        for (int idx = threadIdx.x; idx < g * D; idx += kFastWarps * kWarp) {
+          const int row = idx / D, d = idx - row * D;
+          const int h = kvh * g + row;
+          const float mx = s_m[row];
+          float acc0 = 0.f, acc1 = 0.f;
+          int i = 0;
+          for (; i + 1 < ci.n_chunks; i += 2) {
+            const float w0 = fast_exp2(__ldcg(p.ws_lse + (int64_t)(c0 + i) * Hq + h) - mx);
+            const float w1 = fast_exp2(__ldcg(p.ws_lse + (int64_t)(c0 + i + 1) * Hq + h) - mx);
+            acc0 = fmaf(w0, __ldcg(p.ws_o + ((int64_t)(c0 + i) * Hq + h) * D + d), acc0);
+            acc1 = fmaf(w1, __ldcg(p.ws_o + ((int64_t)(c0 + i + 1) * Hq + h) * D + d), acc1);
+          }
+          if (i < ci.n_chunks) {
+            const float w0 = fast_exp2(__ldcg(p.ws_lse + (int64_t)(c0 + i) * Hq + h) - mx);
+            acc0 = fmaf(w0, __ldcg(p.ws_o + ((int64_t)(c0 + i) * Hq + h) * D + d), acc0);
+          }
           reinterpret_cast<QT*>(p.o)[(int64_t)ci.req * p.o_stride_t + (int64_t)h * p.o_stride_h + d] =
-              from_float<QT>(val * p.v_scale);
-        } else {
-          p.ws_o[((int64_t)c * Hq + h) * D + d] = val;
-          if (d == 0) p.ws_lse[(int64_t)c * Hq + h] = M + log2f(den);
+              from_float<QT>((acc0 + acc1) * s_m[16 + row]);
         }
+        if (threadIdx.x == 0) p.ws_cnt[ci.req * Hkv + kvh] = 0;   // ready for the next launch
       }
     }
     __syncthreads();

@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const Extend
     const uint32_t s_addr = tmem_base + lane_base + kTmemS + t * kBlockKV;
     const uint32_t o_addr = tmem_base + lane_base + kTmemO + t * kD;
     const uint32_t p_row = smem_base + kSmemP + t * kPTileBytes + row * 128;
-    float m_run = -INFINITY, l_run = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;   // m_run in raw (unscaled) score units
 
 #pragma unroll 1
     for (int j = 0; j < n_kv_tiles; ++j) {
@@ -247,30 +247,36 @@ __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const Extend
       mbar_arrive(bar(kBarSFree + t));                        // S_t may be overwritten by the next QK^T
 
       const int kv0 = j * kBlockKV;
-      const bool need_mask = kv0 + kBlockKV - 1 > limit;
-      float mx = m_run;
+      if (kv0 + kBlockKV - 1 > limit) {                       // only the diagonal / ragged tiles need the mask
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float v = __uint_as_float(sv[h][i]) * scale_log2;
-          if (need_mask && kv0 + 32 * h + i > limit) v = -INFINITY;
-          sv[h][i] = __float_as_uint(v);
-          mx = fmaxf(mx, v);
-        }
+        for (int i = 0; i < 64; ++i)
+          if (kv0 + i > limit) sv[i >> 5][i & 31] = 0xff800000u;   // -inf
       }
-      const float corr = fast_exp2(m_run - mx);
-      float sum = 0.f;
+      // running max in raw score units (scale > 0); 3-input max halves the instruction count
+      float mloc = __uint_as_float(sv[0][0]);
+#pragma unroll
+      for (int i = 1; i < 63; i += 2)
+        mloc = fmaxf(mloc, fmaxf(__uint_as_float(sv[i >> 5][i & 31]), __uint_as_float(sv[(i + 1) >> 5][(i + 1) & 31])));
+      mloc = fmaxf(mloc, __uint_as_float(sv[1][31]));
+      float m_new = fmaxf(m_run, mloc);
+      // lazy rescale: keep the old reference max while the new one is < 2^8 larger (P stays <= 256)
+      if ((m_new - m_run) * scale_log2 <= 8.f) m_new = m_run;
+      const float corr = fast_exp2((m_run - m_new) * scale_log2);
+      const float neg = -m_new * scale_log2;
+      float2 sum2 = make_float2(0.f, 0.f);
       uint32_t pk[32];
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        const float p0 = fast_exp2(__uint_as_float(sv[i >> 4][(2 * i) & 31]) - mx);
-        const float p1 = fast_exp2(__uint_as_float(sv[i >> 4][(2 * i + 1) & 31]) - mx);
-        sum += p0 + p1;
-        pk[i] = pack2<QT>(p0, p1);
+        const int a = 2 * i, b = 2 * i + 1;
+        float2 e = ffma2(make_float2(__uint_as_float(sv[a >> 5][a & 31]), __uint_as_float(sv[b >> 5][b & 31])),
+                         make_float2(scale_log2, scale_log2), make_float2(neg, neg));
+        e.x = fast_exp2(e.x);
+        e.y = fast_exp2(e.y);
+        sum2 = fadd2(sum2, e);
+        pk[i] = pack2<QT>(e.x, e.y);
       }
-      l_run = l_run * corr + sum;
-      m_run = mx;
+      l_run = l_run * corr + (sum2.x + sum2.y);
+      m_run = m_new;
 
       if (j > 0) {
         mbar_wait(bar(kBarPVDone + t), (j - 1) & 1, 60 + t);  // O_t stable, P_t buffer free
@@ -323,7 +329,7 @@ __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const Extend
       }
     }
     if (p.lse != nullptr && row_valid)
-      p.lse[(int64_t)(q_tok0 + t * BQ + tok) * p.num_q_heads + kvh * g + head] = (m_run + log2f(l_run)) * kLn2;
+      p.lse[(int64_t)(q_tok0 + t * BQ + tok) * p.num_q_heads + kvh * g + head] = (m_run * scale_log2 + log2f(l_run)) * kLn2;
     tc_fence_before_sync();
   }
 

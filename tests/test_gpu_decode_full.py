@@ -12,9 +12,13 @@ pytestmark = pytest.mark.gpu
 
 def _expected_plan(lens, Hkv, num_ctas, waves, min_chunk, max_chunks):
     total, bs = sum(lens), len(lens)
-    target = num_ctas * waves
-    chunk = max((total * Hkv + target - 1) // target, min_chunk)
-    chunk = (chunk + 63) // 64 * 64
+    per_cta = (total * Hkv + num_ctas - 1) // num_ctas
+    if per_cta <= min_chunk:
+        chunk = per_cta
+    else:
+        w = min(per_cta // min_chunk, waves)
+        chunk = (per_cta + w - 1) // w
+    chunk = (max(chunk, 64) + 63) // 64 * 64
     while total // chunk + bs > max_chunks:
         chunk *= 2
     n = [(L + chunk - 1) // chunk for L in lens]
