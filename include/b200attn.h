@@ -157,11 +157,10 @@ typedef struct b200_decode_args {
   int32_t max_bs, max_chunks;
   float* ws_o;               /* [max_chunks * Hq * Dv] partial outputs */
   float* ws_lse;             /* [max_chunks * Hq] partial log2-sum-exp */
-  int32_t* ws_counters;      /* [max_bs * Hkv] zero-initialised once; the fused merge leaves them zero */
   int32_t num_ctas;          /* persistent grid size (same as in the plan) */
   int32_t kernel;            /* B200_KERNEL_* */
   void* ev_attn_start;       /* optional cudaEvent_t recorded right before the attention kernel */
-  void* ev_attn_stop;        /* optional cudaEvent_t recorded right after it (before the merge) */
+  void* ev_attn_stop;        /* optional cudaEvent_t recorded right after it (before a separate merge) */
 } b200_decode_args;
 
 int b200attn_decode(const b200_decode_args* args, b200_stream_t stream);

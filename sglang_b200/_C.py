@@ -50,7 +50,7 @@ class DecodeArgs(C.Structure):
         ("head_dim_qk", i32), ("head_dim_v", i32), ("q_dtype", i32), ("kv_dtype", i32),
         ("sm_scale", f32), ("k_scale", f32), ("v_scale", f32), ("logit_cap", f32),
         ("plan", vp), ("max_bs", i32), ("max_chunks", i32),
-        ("ws_o", vp), ("ws_lse", vp), ("ws_counters", vp), ("num_ctas", i32), ("kernel", i32),
+        ("ws_o", vp), ("ws_lse", vp), ("num_ctas", i32), ("kernel", i32),
         ("ev_attn_start", vp), ("ev_attn_stop", vp),
     ]
 

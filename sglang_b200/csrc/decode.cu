@@ -70,13 +70,14 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanPar
     } else {
       // tokens x kv-heads each persistent CTA has to stream
       const int64_t per_cta = (total * p.num_kv_heads + p.num_ctas - 1) / p.num_ctas;
-      if (per_cta <= p.min_chunk) {
-        chunk = per_cta;                 // small problem: about one work item per CTA
-      } else {
-        int64_t w = per_cta / p.min_chunk;   // large problem: up to `waves` items per CTA, each >= min_chunk
-        if (w > p.waves) w = p.waves;
-        chunk = (per_cta + w - 1) / w;
-      }
+      // items per CTA: enough that the per-request rounding (<= bs * Hkv ragged items) and the
+      // last-wave quantisation stay small, but never chunks below min_chunk
+      int64_t k = (8 * (int64_t)bs * p.num_kv_heads + p.num_ctas - 1) / p.num_ctas;
+      if (k < 4) k = 4;
+      if (k > p.waves) k = p.waves;
+      if (per_cta < k * p.min_chunk) k = per_cta / p.min_chunk;
+      if (k < 1) k = 1;
+      chunk = (per_cta + k - 1) / k;
       if (chunk < 64) chunk = 64;
     }
     chunk = (chunk + 63) / 64 * 64;
@@ -159,7 +160,6 @@ struct DecodeParams {
   const int32_t* plan;
   float* ws_o;
   float* ws_lse;
-  int32_t* ws_cnt;   // [bs * Hkv] arrival counters of the fused split merge (self-resetting)
   int64_t q_stride_t, q_stride_h, o_stride_t, o_stride_h;
   int64_t k_stride_s, k_stride_h, v_stride_s, v_stride_h;
   int64_t req_to_token_stride;
@@ -355,7 +355,7 @@ extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_)
   B200_CHECK_ARG(a != nullptr, "decode: null args");
   if (a->batch_size == 0) return B200_OK;
   B200_CHECK_ARG(a->q && a->o && a->k_cache && a->v_cache && a->req_to_token && a->req_pool_indices &&
-                     a->seq_lens && a->plan && a->ws_o && a->ws_lse && a->ws_counters,
+                     a->seq_lens && a->plan && a->ws_o && a->ws_lse,
                  "decode: null pointer");
   B200_CHECK_ARG(a->num_q_heads > 0 && a->num_kv_heads > 0 && a->num_q_heads % a->num_kv_heads == 0,
                  "decode: Hq=%d must be a multiple of Hkv=%d", a->num_q_heads, a->num_kv_heads);
@@ -370,7 +370,7 @@ extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_)
   DecodeParams p;
   p.q = a->q; p.o = a->o; p.k_cache = a->k_cache; p.v_cache = a->v_cache;
   p.req_to_token = a->req_to_token; p.req_pool_indices = a->req_pool_indices; p.seq_lens = a->seq_lens;
-  p.plan = a->plan; p.ws_o = a->ws_o; p.ws_lse = a->ws_lse; p.ws_cnt = a->ws_counters;
+  p.plan = a->plan; p.ws_o = a->ws_o; p.ws_lse = a->ws_lse;
   p.q_stride_t = a->q_stride_t; p.q_stride_h = a->q_stride_h;
   p.o_stride_t = a->o_stride_t; p.o_stride_h = a->o_stride_h;
   p.k_stride_s = a->k_stride_s; p.k_stride_h = a->k_stride_h;
@@ -399,7 +399,7 @@ extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_)
   }
   if (rc != B200_OK) return rc;
   if (a->ev_attn_stop) B200_CHECK_CUDA(cudaEventRecord(reinterpret_cast<cudaEvent_t>(a->ev_attn_stop), stream));
-  if (use_fast) return B200_OK;   // the fast kernel merges its splits itself (last-arriving CTA)
+  if (use_fast) return B200_OK;   // the fast path launches its own split merge
   const int64_t rows = (int64_t)a->batch_size * a->num_q_heads;
   const unsigned mgrid = (unsigned)((rows + kMergeWarps - 1) / kMergeWarps);
   if (a->q_dtype == B200_BF16) {

@@ -81,6 +81,64 @@ struct FastCfg {
   static_assert(16 * D * 4 + 256 <= kWarpSmem, "epilogue staging must fit the ring");
 };
 
+// Split merge: one CTA per (request, query head).  out = sum_c 2^(lse_c - M) o_c / sum_c 2^(lse_c - M).
+// Lanes own D/32 consecutive output dims (vector loads); the 4 warps take every 4th chunk and are
+// combined through shared memory, so even 100+ chunks cost only a few dependent L2 round trips.
+template <typename QT, int D>
+__global__ void __launch_bounds__(kFastWarps* kWarp) decode_merge_fast_kernel(const DecodeParams p) {
+  constexpr int kVec = D / 32;
+  __shared__ float s_acc[kFastWarps][D];
+  __shared__ float s_ml[kFastWarps][2];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int Hq = p.num_q_heads;
+  const int req = blockIdx.x / Hq, h = blockIdx.x - req * Hq;
+  const int c0 = p.plan[kPlanHeader + req], n = p.plan[kPlanHeader + req + 1] - c0;
+  if (n <= 1) return;   // single-chunk requests were written by the attention kernel
+  const float* lse = p.ws_lse + (int64_t)c0 * Hq + h;
+  const float* po = p.ws_o + ((int64_t)c0 * Hq + h) * D + lane * kVec;
+  float m = -INFINITY;
+  for (int i = lane; i < n; i += kWarp) m = fmaxf(m, lse[(int64_t)i * Hq]);
+  m = warp_max(m);                                   // every warp computes the global max (n is small)
+  float acc[kVec];
+#pragma unroll
+  for (int e = 0; e < kVec; ++e) acc[e] = 0.f;
+  float den = 0.f;
+#pragma unroll 2
+  for (int i = warp; i < n; i += kFastWarps) {
+    const float w = fast_exp2(lse[(int64_t)i * Hq] - m);
+    const float* src = po + (int64_t)i * Hq * D;
+    float v[kVec];
+    if constexpr (kVec == 2) {
+      const float2 t = *reinterpret_cast<const float2*>(src);
+      v[0] = t.x; v[1] = t.y;
+    } else {
+#pragma unroll
+      for (int e = 0; e < kVec; e += 4) {
+        const float4 t = *reinterpret_cast<const float4*>(src + e);
+        v[e] = t.x; v[e + 1] = t.y; v[e + 2] = t.z; v[e + 3] = t.w;
+      }
+    }
+    den += w;
+#pragma unroll
+    for (int e = 0; e < kVec; ++e) acc[e] = fmaf(w, v[e], acc[e]);
+  }
+#pragma unroll
+  for (int e = 0; e < kVec; ++e) s_acc[warp][lane * kVec + e] = acc[e];
+  if (lane == 0) s_ml[warp][0] = den;
+  __syncthreads();
+  float dsum = 0.f;
+#pragma unroll
+  for (int w = 0; w < kFastWarps; ++w) dsum += s_ml[w][0];
+  const float inv = p.v_scale / dsum;
+  QT* orow = reinterpret_cast<QT*>(p.o) + (int64_t)req * p.o_stride_t + (int64_t)h * p.o_stride_h;
+  for (int d = threadIdx.x; d < D; d += kFastWarps * kWarp) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < kFastWarps; ++w) t += s_acc[w][d];
+    orow[d] = from_float<QT>(t * inv);
+  }
+}
+
 template <int D, int KV, typename QT, bool UPPER>
 __global__ void __launch_bounds__(kFastWarps* kWarp, (FastCfg<D, KV>::kCtaSmem > 110 * 1024) ? 1 : 2)
     decode_mma_kernel(const DecodeParams p) {
@@ -363,54 +421,6 @@ __global__ void __launch_bounds__(kFastWarps* kWarp, (FastCfg<D, KV>::kCtaSmem >
         if (d == 0) p.ws_lse[(int64_t)c * Hq + h] = M + log2f(den);
       }
     }
-    // ---- fused split merge: the CTA that publishes the last partial of (request, kv head) combines them ----
-    if (!final_out) {
-      __shared__ int s_last;
-      __threadfence();                       // partials visible device-wide before the arrival count
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        const int prev = atomicAdd(p.ws_cnt + ci.req * Hkv + kvh, 1);
-        s_last = prev == ci.n_chunks - 1;
-      }
-      __syncthreads();
-      if (s_last) {
-        __threadfence();
-        const int c0 = p.plan[kPlanHeader + ci.req];   // first chunk of this request
-        float* s_m = reinterpret_cast<float*>(smem);   // [16] row max, [16] 1/denominator
-        for (int row = warp; row < g; row += kFastWarps) {
-          const int h = kvh * g + row;
-          float mx = -INFINITY;
-          for (int i = lane; i < ci.n_chunks; i += kWarp) mx = fmaxf(mx, __ldcg(p.ws_lse + (int64_t)(c0 + i) * Hq + h));
-          mx = warp_max(mx);
-          float dn = 0.f;
-          for (int i = lane; i < ci.n_chunks; i += kWarp)
-            dn += fast_exp2(__ldcg(p.ws_lse + (int64_t)(c0 + i) * Hq + h) - mx);
-          dn = warp_sum(dn);
-          if (lane == 0) { s_m[row] = mx; s_m[16 + row] = p.v_scale / dn; }
-        }
-        __syncthreads();
-        for (int idx = threadIdx.x; idx < g * D; idx += kFastWarps * kWarp) {
-          const int row = idx / D, d = idx - row * D;
-          const int h = kvh * g + row;
-          const float mx = s_m[row];
-          float acc0 = 0.f, acc1 = 0.f;
-          int i = 0;
-          for (; i + 1 < ci.n_chunks; i += 2) {
-            const float w0 = fast_exp2(__ldcg(p.ws_lse + (int64_t)(c0 + i) * Hq + h) - mx);
-            const float w1 = fast_exp2(__ldcg(p.ws_lse + (int64_t)(c0 + i + 1) * Hq + h) - mx);
-            acc0 = fmaf(w0, __ldcg(p.ws_o + ((int64_t)(c0 + i) * Hq + h) * D + d), acc0);
-            acc1 = fmaf(w1, __ldcg(p.ws_o + ((int64_t)(c0 + i + 1) * Hq + h) * D + d), acc1);
-          }
-          if (i < ci.n_chunks) {
-            const float w0 = fast_exp2(__ldcg(p.ws_lse + (int64_t)(c0 + i) * Hq + h) - mx);
-            acc0 = fmaf(w0, __ldcg(p.ws_o + ((int64_t)(c0 + i) * Hq + h) * D + d), acc0);
-          }
-          reinterpret_cast<QT*>(p.o)[(int64_t)ci.req * p.o_stride_t + (int64_t)h * p.o_stride_h + d] =
-              from_float<QT>((acc0 + acc1) * s_m[16 + row]);
-        }
-        if (threadIdx.x == 0) p.ws_cnt[ci.req * Hkv + kvh] = 0;   // ready for the next launch
-      }
-    }
     __syncthreads();
     (void)kRows;
   }
@@ -449,6 +459,8 @@ int launch_decode_fast_inst(const DecodeParams& p, int num_ctas, cudaStream_t st
     configured = true;
   }
   kern<<<num_ctas, kFastWarps * kWarp, C::kCtaSmem, stream>>>(p);
+  B200_CHECK_CUDA(cudaGetLastError());
+  decode_merge_fast_kernel<QT, D><<<p.batch_size * p.num_q_heads, kFastWarps * kWarp, 0, stream>>>(p);
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;
 }

@@ -131,7 +131,6 @@ class DecodeWorkspace:
     plan: torch.Tensor   # int32
     ws_o: torch.Tensor   # float32 [max_chunks * Hq * Dv]
     ws_lse: torch.Tensor  # float32 [max_chunks * Hq]
-    ws_cnt: torch.Tensor = None  # int32 [max_bs * Hq] merge arrival counters (kept zero by the kernel)
 
     @staticmethod
     def create(max_bs: int, num_q_heads: int, head_dim_v: int, device, *, num_ctas: int,
@@ -143,7 +142,6 @@ class DecodeWorkspace:
             plan=torch.zeros(n_plan, dtype=torch.int32, device=device),
             ws_o=torch.empty(max_chunks * num_q_heads * head_dim_v, dtype=torch.float32, device=device),
             ws_lse=torch.empty(max_chunks * num_q_heads, dtype=torch.float32, device=device),
-            ws_cnt=torch.zeros(max_bs * num_q_heads, dtype=torch.int32, device=device),
         )
 
 
@@ -207,14 +205,14 @@ def decode_attention(
         q_dtype=dtype_code(q.dtype), kv_dtype=dtype_code(kv_dtype or k_cache.dtype),
         sm_scale=float(sm_scale), k_scale=float(k_scale), v_scale=float(v_scale), logit_cap=float(logit_cap),
         plan=ws.plan.data_ptr(), max_bs=ws.max_bs, max_chunks=ws.max_chunks,
-        ws_o=ws.ws_o.data_ptr(), ws_lse=ws.ws_lse.data_ptr(), ws_counters=ws.ws_cnt.data_ptr(), num_ctas=ws.num_ctas, kernel=kernel,
+        ws_o=ws.ws_o.data_ptr(), ws_lse=ws.ws_lse.data_ptr(), num_ctas=ws.num_ctas, kernel=kernel,
         ev_attn_start=attn_events[0].cuda_event if attn_events else None,
         ev_attn_stop=attn_events[1].cuda_event if attn_events else None,
     )
     if ws.ws_o.numel() < ws.max_chunks * Hq * Dv or ws.ws_lse.numel() < ws.max_chunks * Hq:
         raise ValueError("decode workspace too small for this head configuration")
     _C.check(_C.lib.b200attn_decode(C.byref(a), _stream()), "decode")
-    launch_count += 1  # attention (+ a separate merge launch on the generic path)
+    launch_count += 2  # attention + split merge
     return o
 
 

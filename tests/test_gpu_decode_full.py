@@ -13,11 +13,11 @@ pytestmark = pytest.mark.gpu
 def _expected_plan(lens, Hkv, num_ctas, waves, min_chunk, max_chunks):
     total, bs = sum(lens), len(lens)
     per_cta = (total * Hkv + num_ctas - 1) // num_ctas
-    if per_cta <= min_chunk:
-        chunk = per_cta
-    else:
-        w = min(per_cta // min_chunk, waves)
-        chunk = (per_cta + w - 1) // w
+    k = min(max((8 * bs * Hkv + num_ctas - 1) // num_ctas, 4), waves)
+    if per_cta < k * min_chunk:
+        k = per_cta // min_chunk
+    k = max(k, 1)
+    chunk = (per_cta + k - 1) // k
     chunk = (max(chunk, 64) + 63) // 64 * 64
     while total // chunk + bs > max_chunks:
         chunk *= 2
