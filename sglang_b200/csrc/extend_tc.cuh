@@ -171,28 +171,39 @@ __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const Extend
     }
     cp_async_wait_group<0>();
   } else if (warp == kMmaWarp) {
-    // =========================== MMA issuer (one thread) ========================================
-    if (lane == 0) {
+    // =========================== MMA issuer =====================================================
+    // All 32 lanes run the (warp-uniform) control flow and descriptor arithmetic so it stays on the
+    // uniform datapath; one elected lane issues tcgen05.mma / tcgen05.commit.
+    {
       constexpr int kFmt = dtype_of<QT>::value == B200_BF16 ? 1 : 0;
       constexpr uint32_t idesc_s = umma_idesc_f16(128, kBlockKV, kFmt, 0, 0);
       constexpr uint32_t idesc_pv = umma_idesc_f16(128, kD, kFmt, 0, 1);
+      // descriptor = {hi: SBO 1024 B | version 1 | SWIZZLE_128B, lo: LBO | start address >> 4}
+      constexpr uint32_t kHi = (1024u >> 4) | (1u << 14) | (2u << 29);
+      constexpr uint32_t kLboK = (16u >> 4) << 16;                    // unused by swizzled K-major operands
+      constexpr uint32_t kLboV = ((kBlockKV * 128u) >> 4) << 16;      // V (MN-major): 64-wide d halves 8 KiB apart
+      auto mk = [](uint32_t lo, uint32_t hi) -> uint64_t { return ((uint64_t)hi << 32) | lo; };
+      const bool leader = elect_one();
+      const uint32_t q_lo = ((smem_base + kSmemQ) >> 4) | kLboK;
+      const uint32_t p_lo = ((smem_base + kSmemP) >> 4) | kLboK;
+      const uint32_t kv_lo = (smem_base + kSmemKV) >> 4;
       auto issue_pv = [&](int jj) {
         const int s = jj % kStages;
-        const uint32_t vst = smem_base + kSmemKV + s * kStageBytes + kKTileBytes;
+        const uint32_t v_lo = (kv_lo + s * (kStageBytes >> 4) + (kKTileBytes >> 4)) | kLboV;
+#pragma unroll
         for (int t = 0; t < kQTiles; ++t) {
           mbar_wait(bar(kBarPFull + t), jj & 1, 20 + t);
           tc_fence_after_sync();
-          const uint32_t pst = smem_base + kSmemP + t * kPTileBytes;
 #pragma unroll
           for (int ks = 0; ks < kBlockKV / 16; ++ks) {
-            const uint64_t a = umma_desc_sw128(pst + ks * 32, 16, 1024);
-            // V rows: MN-major B.  16 kv rows per k-step (2 KiB); the two 64-wide d halves are 8 KiB apart.
-            const uint64_t b = umma_desc_sw128(vst + ks * 2048, kBlockKV * 128, 1024);
-            umma_f16_ss(tmem_base + kTmemO + t * kD, a, b, idesc_pv, (jj > 0 || ks > 0) ? 1u : 0u);
+            // A = P_t (K-major, 32 B per k-step); B = 16 V rows per k-step (2 KiB)
+            const uint64_t a = mk(p_lo + t * (kPTileBytes >> 4) + ks * 2, kHi);
+            const uint64_t b = mk(v_lo + ks * (2048 >> 4), kHi);
+            if (leader) umma_f16_ss(tmem_base + kTmemO + t * kD, a, b, idesc_pv, (jj > 0 || ks > 0) ? 1u : 0u);
           }
-          umma_commit(bar(kBarPVDone + t));
+          if (leader) umma_commit(bar(kBarPVDone + t));
         }
-        umma_commit(bar(kBarKVEmpty + s));
+        if (leader) umma_commit(bar(kBarKVEmpty + s));
       };
       mbar_wait(bar(kBarQFull), 0, 30);
       tc_fence_after_sync();
@@ -201,20 +212,20 @@ __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const Extend
         const int s = j % kStages;
         mbar_wait(bar(kBarKVFull + s), (j / kStages) & 1, 31 + s);
         tc_fence_after_sync();
-        const uint32_t kst = smem_base + kSmemKV + s * kStageBytes;
+        const uint32_t k_lo = (kv_lo + s * (kStageBytes >> 4)) | kLboK;
+#pragma unroll
         for (int t = 0; t < kQTiles; ++t) {
           if (j > 0) {
             mbar_wait(bar(kBarSFree + t), (j - 1) & 1, 40 + t);
             tc_fence_after_sync();
           }
-          const uint32_t qst = smem_base + kSmemQ + t * kQTileBytes;
 #pragma unroll
           for (int ks = 0; ks < kD / 16; ++ks) {
-            const uint64_t a = umma_desc_sw128(qst + (ks >> 2) * (128 * 128) + (ks & 3) * 32, 16, 1024);
-            const uint64_t b = umma_desc_sw128(kst + (ks >> 2) * (kBlockKV * 128) + (ks & 3) * 32, 16, 1024);
-            umma_f16_ss(tmem_base + kTmemS + t * kBlockKV, a, b, idesc_s, ks > 0 ? 1u : 0u);
+            const uint64_t a = mk(q_lo + t * (kQTileBytes >> 4) + (ks >> 2) * ((128 * 128) >> 4) + (ks & 3) * 2, kHi);
+            const uint64_t b = mk(k_lo + (ks >> 2) * ((kBlockKV * 128) >> 4) + (ks & 3) * 2, kHi);
+            if (leader) umma_f16_ss(tmem_base + kTmemS + t * kBlockKV, a, b, idesc_s, ks > 0 ? 1u : 0u);
           }
-          umma_commit(bar(kBarSFull + t));
+          if (leader) umma_commit(bar(kBarSFull + t));
         }
         if (j > 0) issue_pv(j - 1);
       }
