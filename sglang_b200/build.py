@@ -44,7 +44,7 @@ def _stale(target: Path, deps) -> bool:
 
 
 def build_cuda(force: bool = False, verbose: bool = False) -> Path:
-    deps = sorted(CSRC.glob("*.cu")) + sorted(CSRC.glob("*.cuh")) + [REPO_DIR / "include" / "b200attn.h"]
+    deps = sorted(CSRC.glob("*.cu")) + sorted(CSRC.glob("*.cuh")) + sorted(CSRC.glob("*.inc")) + [REPO_DIR / "include" / "b200attn.h"]
     if not force and not _stale(LIB_PATH, deps):
         return LIB_PATH
     LIB_DIR.mkdir(parents=True, exist_ok=True)

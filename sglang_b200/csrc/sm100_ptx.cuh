@@ -76,6 +76,19 @@ __device__ __forceinline__ void cp_async_commit_group() { asm volatile("cp.async
 template <int N> __device__ __forceinline__ void cp_async_wait_group() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
+// The mbarrier gets one arrival (already counted in its expected count) once every cp.async this thread
+// has issued so far has landed: the producer never blocks on its own loads.
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// ------------------------------------------------------------------ register re-allocation between warpgroups
+template <int N> __device__ __forceinline__ void setmaxnreg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
+}
+template <int N> __device__ __forceinline__ void setmaxnreg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
+}
 
 // ------------------------------------------------------------------ TMEM
 template <int kCols> __device__ __forceinline__ void tmem_alloc(uint32_t smem_result_addr) {
@@ -96,6 +109,16 @@ __device__ __forceinline__ void umma_f16_ss(uint32_t d_tmem, uint64_t a_desc, ui
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem desc]: A is M lanes x (K/2) 32-bit columns, two 16-bit K elements per column.
+__device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
 // arrives on the mbarrier once every tcgen05 op issued so far by this thread has completed
@@ -150,6 +173,26 @@ __device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
   asm("add.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
   asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
   return d;
+}
+
+// 2^x for a pair of fp32 on the FMA/ALU pipes instead of the 16-lane/clk MUFU: round-to-nearest split
+// x = n + f (|f| <= 0.5) through the 1.5*2^23 trick, degree-3 minimax of 2^f (max rel. error 7.5e-5, far
+// below the bf16/f16 rounding of P), exponent patched in with one integer multiply-add.  x is clamped
+// at -126 (masked scores are -inf); the caller guarantees x <= ~100.
+__device__ __forceinline__ float2 exp2_poly2(float2 x) {
+  x.x = fmaxf(x.x, -126.f);
+  x.y = fmaxf(x.y, -126.f);
+  const float2 t = fadd2(x, make_float2(12582912.f, 12582912.f));
+  const float2 nf = fadd2(t, make_float2(-12582912.f, -12582912.f));
+  const float2 f = ffma2(nf, make_float2(-1.f, -1.f), x);
+  float2 p = ffma2(make_float2(0.055171407759189606f, 0.055171407759189606f), f,
+                   make_float2(0.24261075258255005f, 0.24261075258255005f));
+  p = ffma2(p, f, make_float2(0.6932609677314758f, 0.6932609677314758f));
+  p = ffma2(p, f, make_float2(0.9999281167984009f, 0.9999281167984009f));
+  float2 r;
+  r.x = __int_as_float(__float_as_int(t.x) * 0x800000 + __float_as_int(p.x));
+  r.y = __int_as_float(__float_as_int(t.y) * 0x800000 + __float_as_int(p.y));
+  return r;
 }
 
 // ------------------------------------------------------------------ UMMA descriptors
