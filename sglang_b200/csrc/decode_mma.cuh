@@ -71,7 +71,7 @@ struct FastCfg {
   static constexpr int kCpr = kRowB / 16;                // 16-byte chunks per row
   static constexpr int kTileB = kTileTok * kRowB;        // K (or V) bytes per stage
   static constexpr int kStageB = 2 * kTileB;
-  static constexpr int kStagesRaw = kWarpSmemTarget / kStageB;
+  static constexpr int kStagesRaw = (kFp8 ? 16384 : kWarpSmemTarget) / kStageB;   // FP8: 3 CTAs per SM
   static constexpr int kStages = kStagesRaw < 3 ? 3 : (kStagesRaw > 8 ? 8 : kStagesRaw);
   static constexpr int kWarpSmem = kStages * kStageB;
   static constexpr int kCtaSmem = kFastWarps * kWarpSmem;
@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(kFastWarps* kWarp) decode_merge_fast_kernel(co
 }
 
 template <int D, int KV, typename QT, bool UPPER>
-__global__ void __launch_bounds__(kFastWarps* kWarp, (FastCfg<D, KV>::kCtaSmem > 110 * 1024) ? 1 : 2)
+__global__ void __launch_bounds__(kFastWarps* kWarp, (FastCfg<D, KV>::kCtaSmem > 110 * 1024) ? 1 : ((FastCfg<D, KV>::kCtaSmem <= 72 * 1024) ? 3 : 2))
     decode_mma_kernel(const DecodeParams p) {
   using C = FastCfg<D, KV>;
   using CT = typename std::conditional<C::kFp8, __half, QT>::type;  // MMA operand type
@@ -437,8 +437,8 @@ bool decode_fast_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype
 }
 
 int decode_fast_ctas_per_sm(int head_dim, int kv_dtype) {
-  (void)kv_dtype;
-  return head_dim >= 256 ? 1 : 2;
+  if (head_dim >= 256) return 1;
+  return (kv_dtype == B200_FP8_E4M3 && head_dim == 128) ? 3 : 2;
 }
 
 bool decode_fast_layout_ok(const DecodeParams& p, int kv_dtype) {

@@ -158,7 +158,8 @@ bool extend_fast_layout_ok(const ExtendParams& p, int kv_dtype) {
   auto a16 = [](const void* ptr) { return ((uintptr_t)ptr & 15) == 0; };
   return a16(p.k_cache) && a16(p.v_cache) && a16(p.q) && a16(p.o) && p.k_stride_s % 8 == 0 &&
          p.k_stride_h % 8 == 0 && p.v_stride_s % 8 == 0 && p.v_stride_h % 8 == 0 && p.q_stride_t % 8 == 0 &&
-         p.q_stride_h % 8 == 0 && p.o_stride_t % 8 == 0 && p.o_stride_h % 8 == 0;
+         p.q_stride_h % 8 == 0 && p.o_stride_t % 8 == 0 && p.o_stride_h % 8 == 0 &&
+         p.k_stride_s > 0 && p.v_stride_s > 0 && p.k_stride_s < (1ll << 30) && p.v_stride_s < (1ll << 30);
 }
 
 template <typename QT, int kEmu>
