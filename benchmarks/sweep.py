@@ -59,7 +59,7 @@ def decode_case(name, bs, L, Hq, Hkv, D, pool_dtype, page, iters, ragged=False):
     rpi = torch.arange(1, bs + 1, device=dev)
     sm, _, _ = ops.device_info()
     ws = ops.DecodeWorkspace.create(bs, Hq, D, dev, num_ctas=sm * ops.decode_ctas_per_sm(D, pool_dtype))
-    ops.decode_plan(ws, lens, Hkv)
+    ops.decode_plan(ws, lens, Hkv, items_per_chunk=ops.decode_items_per_chunk(Hq, Hkv, D, D, torch.bfloat16, pool_dtype))
 
     def fn():
         ops.decode_attention(q, o, kp, vp, rtt, rpi, lens, ws, D**-0.5, kv_dtype=pool_dtype)

@@ -118,8 +118,9 @@ typedef struct b200_decode_plan_args {
   int32_t max_chunks;
   int32_t num_kv_heads;      /* work multiplicity per chunk */
   int32_t num_ctas;          /* persistent CTAs the decode kernel will run */
-  int32_t waves;             /* most work items per CTA (load-balance granularity) */
-  int32_t min_chunk_tokens;  /* preferred smallest chunk (tokens x kv heads per item), multiple of 64 */
+  int32_t waves;             /* most rounds (work items per CTA) the planner considers, <= 32 */
+  int32_t min_chunk_tokens;  /* smallest chunk the planner may choose, multiple of 16; min_chunk/4 is also its
+                                per-item overhead estimate (in tokens) when it ranks candidate chunk sizes */
   int32_t fixed_chunk_tokens;/* > 0 overrides the heuristic (deterministic splits) */
   int32_t* plan;             /* device, b200attn_decode_plan_ints() ints */
 } b200_decode_plan_args;
@@ -169,6 +170,11 @@ int b200attn_decode_fast_supported(int32_t head_dim_qk, int32_t head_dim_v, int3
                                    int32_t q_dtype, int32_t kv_dtype);
 /* persistent CTAs per SM the fast decode kernel is tuned for */
 int b200attn_decode_ctas_per_sm(int32_t head_dim, int32_t kv_dtype);
+/* Work items the attention kernel creates per split chunk: num_kv_heads for the per-head kernel,
+ * num_kv_heads / 4 when the head-group kernel (4 adjacent kv heads per CTA) covers the shape.  Pass it
+ * as b200_decode_plan_args.num_kv_heads so that the planner balances the persistent grid. */
+int b200attn_decode_items_per_chunk(int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim_qk,
+                                    int32_t head_dim_v, int32_t q_dtype, int32_t kv_dtype);
 
 /* ------------------------------------------------------------------------ *
  * Extend (prefill over a cached prefix) planner: qo_indptr = exclusive scan of

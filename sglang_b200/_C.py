@@ -91,6 +91,7 @@ SYMBOLS = {
     "b200attn_decode": (C.c_int, [C.POINTER(DecodeArgs), vp]),
     "b200attn_decode_fast_supported": (C.c_int, [i32] * 5),
     "b200attn_decode_ctas_per_sm": (C.c_int, [i32, i32]),
+    "b200attn_decode_items_per_chunk": (C.c_int, [i32] * 6),
     "b200attn_extend_plan_ints": (i64, [i32, i32]),
     "b200attn_extend_plan": (C.c_int, [C.POINTER(ExtendPlanArgs), vp]),
     "b200attn_extend": (C.c_int, [C.POINTER(ExtendArgs), vp]),

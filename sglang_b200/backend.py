@@ -77,6 +77,8 @@ class B200AttnBackend(_Base):
         self.decode_kernel = ops.KERNEL_AUTO
         self.extend_kernel = ops.KERNEL_AUTO
         self.decode_ctas = sm_count * ops.decode_ctas_per_sm(self.head_dim, self.kv_dtype)
+        self._decode_items = ops.decode_items_per_chunk(self.num_head, self.num_kv_head, self.head_dim,
+                                                        self.v_head_dim, self._q_dtype, self.kv_dtype)
         self.decode_ws = ops.DecodeWorkspace.create(
             self.max_bs, self.num_head, self.v_head_dim, dev, num_ctas=self.decode_ctas, waves=self.DECODE_WAVES)
         self.extend_ws: Optional[ops.ExtendWorkspace] = None
@@ -117,7 +119,7 @@ class B200AttnBackend(_Base):
             return
         if mode.is_decode():
             ops.decode_plan(self.decode_ws, forward_batch.seq_lens[: forward_batch.batch_size],
-                            self.num_kv_head, waves=self.DECODE_WAVES)
+                            self.num_kv_head, waves=self.DECODE_WAVES, items_per_chunk=self._decode_items)
         else:
             ops.extend_plan(self.extend_ws, forward_batch.extend_seq_lens, self._extend_block_q)
 
@@ -130,7 +132,9 @@ class B200AttnBackend(_Base):
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
         if max_bs > self.decode_ws.max_bs:
             self.max_bs = max_bs
-            self.decode_ws = ops.DecodeWorkspace.create(
+            self._decode_items = ops.decode_items_per_chunk(self.num_head, self.num_kv_head, self.head_dim,
+                                                        self.v_head_dim, self._q_dtype, self.kv_dtype)
+        self.decode_ws = ops.DecodeWorkspace.create(
                 max_bs, self.num_head, self.v_head_dim, self.device, num_ctas=self.decode_ctas,
                 waves=self.DECODE_WAVES)
 

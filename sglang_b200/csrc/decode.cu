@@ -13,8 +13,11 @@
 //   sum_r L_r * Hkv * (Dk + Dv) * s_kv + sum_r L_r * 4 + bs * Hq * (Dk + Dv) * 2.
 #include <type_traits>
 
+#include <cstdlib>
+
 #include "common.cuh"
 #include "generic_attn.cuh"
+#include "sm100_ptx.cuh"
 
 namespace b200 {
 namespace {
@@ -53,6 +56,7 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanPar
   __shared__ int64_t s_red[32];
   __shared__ int32_t s_warp_tot[32];
   __shared__ int32_t s_chunk, s_carry;
+  __shared__ int64_t s_cost[32], s_cand[32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int bs = p.batch_size;
 
@@ -63,24 +67,59 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanPar
   }
   const int64_t total = block_sum_i64(local, s_red);
 
+  // Candidate m = warp + 1 "rounds": the smallest chunk (multiple of 16 tokens, >= min_chunk) whose item
+  // count  items(chunk) = G * sum_r ceil(L_r / chunk)  fits m * num_ctas, found by bisection (items() is
+  // monotone).  Cost model: rounds actually needed x (chunk + per-item overhead); lowest cost wins, ties go
+  // to fewer rounds.  Every warp works alone (no block barrier inside the search).
+  {
+    const int m = warp + 1;
+    int64_t maxl = 0;
+    for (int r = lane; r < bs; r += 32) {
+      const int64_t L = load_index(p.seq_lens, p.seq_lens_is_i64, r);
+      maxl = L > maxl ? L : maxl;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const int64_t t = __shfl_xor_sync(0xffffffffu, maxl, o);
+      maxl = t > maxl ? t : maxl;
+    }
+    auto items = [&](int64_t chunk) -> int64_t {
+      int64_t n = 0;
+      for (int r = lane; r < bs; r += 32) {
+        const int64_t L = load_index(p.seq_lens, p.seq_lens_is_i64, r);
+        if (L > 0) n += (L + chunk - 1) / chunk;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+      return n * p.num_kv_heads;
+    };
+    const int64_t u_min = (p.min_chunk + 15) / 16;
+    int64_t u_max = (maxl + 15) / 16;
+    if (u_max < u_min) u_max = u_min;
+    const int64_t cap = (int64_t)m * p.num_ctas;
+    int64_t lo = u_min, hi = u_max;            // smallest u in [u_min, u_max] with items(16 u) <= cap, else u_max
+    while (lo < hi) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (items(16 * mid) <= cap) hi = mid; else lo = mid + 1;
+    }
+    const int64_t chunk = 16 * lo;
+    const int64_t rounds = (items(chunk) + p.num_ctas - 1) / p.num_ctas;
+    if (lane == 0) {
+      s_cost[warp] = (m <= p.waves) ? rounds * (chunk + p.min_chunk / 4) : (int64_t(1) << 62);
+      s_cand[warp] = chunk;
+    }
+  }
+  __syncthreads();
   if (tid == 0) {
     int64_t chunk;
     if (p.fixed_chunk > 0) {
       chunk = p.fixed_chunk;
     } else {
-      // tokens x kv-heads each persistent CTA has to stream
-      const int64_t per_cta = (total * p.num_kv_heads + p.num_ctas - 1) / p.num_ctas;
-      // items per CTA: enough that the per-request rounding (<= bs * Hkv ragged items) and the
-      // last-wave quantisation stay small, but never chunks below min_chunk
-      int64_t k = (8 * (int64_t)bs * p.num_kv_heads + p.num_ctas - 1) / p.num_ctas;
-      if (k < 4) k = 4;
-      if (k > p.waves) k = p.waves;
-      if (per_cta < k * p.min_chunk) k = per_cta / p.min_chunk;
-      if (k < 1) k = 1;
-      chunk = (per_cta + k - 1) / k;
-      if (chunk < 64) chunk = 64;
+      int best = 0;
+      for (int w = 1; w < 32; ++w)
+        if (s_cost[w] < s_cost[best]) best = w;
+      chunk = s_cand[best];
     }
-    chunk = (chunk + 63) / 64 * 64;
     // capacity: sum_r ceil(L_r / chunk) <= total / chunk + bs must fit the work list
     while (total / chunk + bs > p.max_chunks && chunk < (int64_t(1) << 30)) chunk *= 2;
     s_chunk = (int32_t)chunk;
@@ -187,8 +226,9 @@ __device__ __forceinline__ ChunkInfo load_chunk(const DecodeParams& p, int c) {
   const int off = chunk_offset[ci.req];
   ci.n_chunks = chunk_offset[ci.req + 1] - off;
   const int64_t L = load_index(p.seq_lens, p.seq_lens_is_i64, ci.req);
-  // equal-sized chunks inside a request: n = ceil(L / chunk) pieces of roundup64(ceil(L / n)) tokens
-  const int cs = (int)(((L + ci.n_chunks - 1) / ci.n_chunks + 63) / 64 * 64);
+  // equal-sized chunks inside a request: n = ceil(L / chunk) pieces of roundup16(ceil(L / n)) tokens
+  // (16 = the kernels' token tile; cs <= chunk because chunk is a multiple of 16, so (n-1) cs < L)
+  const int cs = (int)(((L + ci.n_chunks - 1) / ci.n_chunks + 15) / 16 * 16);
   ci.start = (c - off) * cs;
   const int64_t rem = L - ci.start;
   ci.n_tok = (int)(rem < cs ? rem : cs);
@@ -295,6 +335,7 @@ __global__ void __launch_bounds__(kMergeWarps* kWarp) decode_merge_kernel(const 
 
 // fast path lives in its own translation unit section
 #include "decode_mma.cuh"
+#include "decode_hg.cuh"
 
 namespace {
 
@@ -328,8 +369,9 @@ extern "C" int b200attn_decode_plan(const b200_decode_plan_args* a, b200_stream_
   B200_CHECK_ARG(a->max_chunks > a->batch_size, "decode_plan: max_chunks %d must exceed bs %d",
                  a->max_chunks, a->batch_size);
   B200_CHECK_ARG(a->num_kv_heads > 0 && a->num_ctas > 0 && a->waves > 0, "decode_plan: bad grid hints");
-  B200_CHECK_ARG(a->min_chunk_tokens > 0 && a->min_chunk_tokens % 64 == 0,
-                 "decode_plan: min_chunk_tokens must be a positive multiple of 64");
+  B200_CHECK_ARG(a->min_chunk_tokens > 0 && a->min_chunk_tokens % 16 == 0,
+                 "decode_plan: min_chunk_tokens must be a positive multiple of 16");
+  B200_CHECK_ARG(a->fixed_chunk_tokens % 16 == 0, "decode_plan: fixed_chunk_tokens must be a multiple of 16");
   B200_CHECK_ARG(a->fixed_chunk_tokens >= 0, "decode_plan: negative fixed_chunk_tokens");
   PlanParams p;
   p.seq_lens = a->seq_lens; p.plan = a->plan; p.seq_lens_is_i64 = a->seq_lens_is_i64;
@@ -346,8 +388,37 @@ extern "C" int b200attn_decode_fast_supported(int32_t dqk, int32_t dv, int32_t g
   return b200::decode_fast_supported(dqk, dv, group, q_dtype, kv_dtype) ? 1 : 0;
 }
 
+namespace b200 {
+namespace {
+// B200ATTN_DECODE_HG=0 forces the per-head kernel (A/B measurements); default on.
+bool decode_hg_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200ATTN_DECODE_HG");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
+bool decode_hg_shape_ok(int hq, int hkv, int dqk, int dv, int q_dtype, int kv_dtype) {
+  if (!decode_hg_enabled() || hkv <= 0 || hq % hkv != 0 || hkv % kHG != 0) return false;
+  if (!decode_fast_supported(dqk, dv, hq / hkv, q_dtype, kv_dtype)) return false;
+  return !(dqk == 256 && kv_dtype != B200_FP8_E4M3);
+}
+}  // namespace
+}  // namespace b200
+
 extern "C" int b200attn_decode_ctas_per_sm(int32_t head_dim, int32_t kv_dtype) {
-  return b200::decode_fast_ctas_per_sm(head_dim, kv_dtype);
+  const int a = b200::decode_fast_ctas_per_sm(head_dim, kv_dtype);
+  const int b = b200::decode_hg_enabled() && (head_dim == 64 || head_dim == 128 || head_dim == 256)
+                    ? b200::decode_hg_ctas_per_sm(head_dim, kv_dtype) : 0;
+  return a > b ? a : b;
+}
+
+extern "C" int b200attn_decode_items_per_chunk(int32_t num_q_heads, int32_t num_kv_heads, int32_t dqk, int32_t dv,
+                                               int32_t q_dtype, int32_t kv_dtype) {
+  if (b200::decode_hg_shape_ok(num_q_heads, num_kv_heads, dqk, dv, q_dtype, kv_dtype))
+    return num_kv_heads / b200::kHG;
+  return num_kv_heads;
 }
 
 extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_) {
@@ -390,7 +461,10 @@ extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_)
   const bool use_fast = fast_ok && a->kernel != B200_KERNEL_GENERIC && a->logit_cap == 0.f;
   int rc;
   if (a->ev_attn_start) B200_CHECK_CUDA(cudaEventRecord(reinterpret_cast<cudaEvent_t>(a->ev_attn_start), stream));
-  if (use_fast) {
+  const bool use_hg = use_fast && decode_hg_enabled() && decode_hg_supported(p, a->q_dtype, a->kv_dtype);
+  if (use_hg) {
+    rc = launch_decode_hg(p, a->q_dtype, a->kv_dtype, a->num_ctas, stream);
+  } else if (use_fast) {
     rc = launch_decode_fast(p, a->q_dtype, a->kv_dtype, a->num_ctas, stream);
   } else if (a->q_dtype == B200_BF16) {
     rc = launch_generic<__nv_bfloat16>(p, a->kv_dtype, a->num_ctas, stream);

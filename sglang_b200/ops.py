@@ -146,10 +146,18 @@ class DecodeWorkspace:
 
 
 def decode_plan(ws: DecodeWorkspace, seq_lens: torch.Tensor, num_kv_heads: int, *, waves: int = 16,
-                min_chunk_tokens: int = 512, fixed_chunk_tokens: int = 0) -> None:
-    """Per-forward split-KV work list, built on the device (no host sync)."""
+                min_chunk_tokens: int = 512, fixed_chunk_tokens: int = 0,
+                items_per_chunk: Optional[int] = None) -> None:
+    """Per-forward split-KV work list, built on the device (no host sync).
+
+    `items_per_chunk` (see `decode_items_per_chunk`) replaces `num_kv_heads` as the grid hint when the
+    head-group kernel will run: an item then covers 4 kv heads, so the smallest useful chunk shrinks by
+    the same factor."""
     global launch_count
     _need_cuda(seq_lens, ws.plan)
+    if items_per_chunk is not None and 0 < items_per_chunk < num_kv_heads:
+        min_chunk_tokens = max(64, (min_chunk_tokens * items_per_chunk // num_kv_heads) // 16 * 16)
+        num_kv_heads = items_per_chunk
     a = _C.DecodePlanArgs(
         seq_lens=seq_lens.data_ptr(), seq_lens_is_i64=_index_kind(seq_lens, "seq_lens"),
         batch_size=seq_lens.shape[0], max_bs=ws.max_bs, max_chunks=ws.max_chunks,
@@ -219,6 +227,14 @@ def decode_attention(
 def decode_fast_supported(head_dim_qk: int, head_dim_v: int, group: int, q_dtype, kv_dtype) -> bool:
     return bool(_C.lib.b200attn_decode_fast_supported(head_dim_qk, head_dim_v, group, dtype_code(q_dtype),
                                                       dtype_code(kv_dtype)))
+
+
+def decode_items_per_chunk(num_q_heads: int, num_kv_heads: int, head_dim_qk: int, head_dim_v: int,
+                           q_dtype, kv_dtype) -> int:
+    """Work items per split chunk (kv heads, or kv-head groups of 4 for the head-group kernel): the
+    `num_kv_heads` grid hint `decode_plan` wants."""
+    return int(_C.lib.b200attn_decode_items_per_chunk(num_q_heads, num_kv_heads, head_dim_qk, head_dim_v,
+                                                      dtype_code(q_dtype), dtype_code(kv_dtype)))
 
 
 def decode_ctas_per_sm(head_dim: int, kv_dtype) -> int:

@@ -10,15 +10,30 @@ from oracle import torch_native_ref as ref
 pytestmark = pytest.mark.gpu
 
 
-def _expected_plan(lens, Hkv, num_ctas, waves, min_chunk, max_chunks):
+def _expected_plan(lens, G, num_ctas, waves, min_chunk, max_chunks):
+    """numpy restatement of decode_plan_kernel: candidate m = 1..waves rounds, smallest 16-multiple chunk
+    whose item count fits m * num_ctas (bisection), cost = rounds * (chunk + min_chunk / 4)."""
     total, bs = sum(lens), len(lens)
-    per_cta = (total * Hkv + num_ctas - 1) // num_ctas
-    k = min(max((8 * bs * Hkv + num_ctas - 1) // num_ctas, 4), waves)
-    if per_cta < k * min_chunk:
-        k = per_cta // min_chunk
-    k = max(k, 1)
-    chunk = (per_cta + k - 1) // k
-    chunk = (max(chunk, 64) + 63) // 64 * 64
+
+    def items(chunk):
+        return G * sum((L + chunk - 1) // chunk for L in lens if L > 0)
+
+    u_min = (min_chunk + 15) // 16
+    u_max = max(u_min, (max(lens + [0]) + 15) // 16)
+    best = None
+    for m in range(1, min(waves, 32) + 1):
+        lo, hi = u_min, u_max
+        while lo < hi:
+            mid = (lo + hi) >> 1
+            if items(16 * mid) <= m * num_ctas:
+                hi = mid
+            else:
+                lo = mid + 1
+        chunk = 16 * lo
+        cost = ((items(chunk) + num_ctas - 1) // num_ctas) * (chunk + min_chunk // 4)
+        if best is None or cost < best[0]:
+            best = (cost, chunk)
+    chunk = best[1]
     while total // chunk + bs > max_chunks:
         chunk *= 2
     n = [(L + chunk - 1) // chunk for L in lens]
