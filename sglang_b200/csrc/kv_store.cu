@@ -6,9 +6,10 @@
 // (kernels/jit/csrc/attention/fused_fp8_qkv_kv_cache.cuh:58-90).
 //
 // Layout: one warp moves one 256-element segment of one K row and the matching
-// V row segment; every lane owns 8 consecutive elements = one 16-byte load and one
-// 16-byte (same dtype) or 8-byte (FP8) store.  A CTA of 4 warps therefore covers
-// up to 2 KiB of a bf16 row per row-segment group; the grid is tokens x segments.
+// V row segment; every lane owns 8 consecutive elements of each = two 16-byte loads in
+// flight and two 16-byte (same dtype) or 8-byte (FP8) stores.  The grid is tokens x segments.
+// FP8-e4m3 uses the hardware RNE pack (cvt.rn.satfinite.e4m3x2.f32) and falls back to the scalar
+// bit-exact restatement of torch's non-saturating cast only for vectors holding |x| > 464 / Inf / NaN.
 // HBM-bound byte work: algorithmic bytes = T * (Ek + Ev) * (src + dst itemsize) + T * 8.
 #include "common.cuh"
 
@@ -29,7 +30,7 @@ struct StoreParams {
   int64_t num_tokens;
   int64_t size_limit, skip_index;
   int32_t k_row_elems, v_row_elems;
-  int32_t k_segs, segs;                        // segments in a K row, K+V segments per token
+  int32_t k_segs, segs;                        // segments in a K row, warps (segments) per token
   float k_scale, v_scale;
   int32_t loc_is_i64;
 };
@@ -75,19 +76,48 @@ __device__ __forceinline__ auto convert_elem(uint16_t bits, float scale, bool sc
   return from_float<DST>(f);
 }
 
+// two floats -> two e4m3 bytes (hi -> bits 15:8, lo -> bits 7:0), RNE, saturating (the caller has already
+// ruled out everything torch's non-saturating cast would turn into NaN, i.e. |x| > 464)
+__device__ __forceinline__ uint32_t pack_e4m3x2_sat(float hi, float lo) {
+  uint16_t r;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
+// Convert + store the 8 elements of one 16-byte source vector (already loaded).
 template <typename SRC, typename DST>
-__device__ __forceinline__ void move_vec8(const SRC* src, DST* dst, float scale, bool scaled) {
-  const uint4 raw = ld_stream_16(src);
+__device__ __forceinline__ void finish_vec8(const uint4 raw, DST* dst, float scale, bool scaled) {
   if constexpr (sizeof(DST) == 2 && dtype_of<SRC>::value == dtype_of<DST>::value) {
     st_16(dst, raw);  // byte copy
   } else if constexpr (sizeof(DST) == 1) {
     const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
     uint32_t out[2] = {0u, 0u};
+    if constexpr (dtype_of<DST>::value == B200_FP8_E4M3) {
+      // Hardware RNE pack is bit-identical to torch's cast for |x| <= 464 (464 ties to 448 in both); larger
+      // magnitudes, Inf and NaN must become NaN | sign, which the saturating instruction cannot produce:
+      // those vectors (never seen with sane K/V) take the bit-exact scalar restatement below.
+      float f[8];
+      uint32_t amax = 0u;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const uint16_t bits = (uint16_t)(w[i >> 1] >> ((i & 1) * 16));
-      const uint32_t byte = convert_elem<SRC, DST>(bits, scale, scaled).x;
-      out[i >> 2] |= byte << ((i & 3) * 8);
+      for (int i = 0; i < 8; ++i) {
+        f[i] = src_bits_to_float<SRC>((uint16_t)(w[i >> 1] >> ((i & 1) * 16)));
+        if (scaled) f[i] = round_to_src<SRC>(__fdiv_rn(f[i], scale));
+        amax = max(amax, __float_as_uint(f[i]) & 0x7fffffffu);
+      }
+      if (amax <= 0x43E80000u) {  // 464.0f
+        out[0] = pack_e4m3x2_sat(f[1], f[0]) | (pack_e4m3x2_sat(f[3], f[2]) << 16);
+        out[1] = pack_e4m3x2_sat(f[5], f[4]) | (pack_e4m3x2_sat(f[7], f[6]) << 16);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) out[i >> 2] |= (uint32_t)float_to_e4m3_bits(f[i]) << ((i & 3) * 8);
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const uint16_t bits = (uint16_t)(w[i >> 1] >> ((i & 1) * 16));
+        const uint32_t byte = convert_elem<SRC, DST>(bits, scale, scaled).x;
+        out[i >> 2] |= byte << ((i & 3) * 8);
+      }
     }
     st_8(dst, make_uint2(out[0], out[1]));
   } else {
@@ -119,13 +149,24 @@ __device__ __forceinline__ void move_scalar(const SRC* src, DST* dst, int n, int
 }
 
 // kVecOK: rows, strides and base pointers are all multiples of 8 elements.
+// One warp = segment `s` of BOTH the K row and the V row of one token: the two 16-byte loads are issued
+// back to back (the slot lookup, needed only for the stores, overlaps them).
 template <typename SRC, typename DST, bool kVecOK>
 __global__ void __launch_bounds__(kStoreWarps* kWarp) store_kv_kernel(const StoreParams p) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = (int64_t)blockIdx.x * kStoreWarps + (threadIdx.x >> 5);
   const int64_t token = warp / p.segs;
   if (token >= p.num_tokens) return;
-  const int seg = (int)(warp - token * p.segs);
+  const int s = (int)(warp - token * p.segs);
+  const int k_rem = p.k_row_elems - s * kSegElems, v_rem = p.v_row_elems - s * kSegElems;
+  const SRC* k_src = reinterpret_cast<const SRC*>(p.k) + token * p.k_src_stride + (int64_t)s * kSegElems;
+  const SRC* v_src = reinterpret_cast<const SRC*>(p.v) + token * p.v_src_stride + (int64_t)s * kSegElems;
+  uint4 k_raw = make_uint4(0, 0, 0, 0), v_raw = make_uint4(0, 0, 0, 0);
+  const bool k_on = lane * kVec < k_rem, v_on = lane * kVec < v_rem;
+  if constexpr (kVecOK) {
+    if (k_on) k_raw = ld_stream_16(k_src + lane * kVec);
+    if (v_on) v_raw = ld_stream_16(v_src + lane * kVec);
+  }
   const int64_t slot = load_index(p.loc, p.loc_is_i64, token);
   if (slot == p.skip_index) return;  // reserved sink slot: padded CUDA-graph rows land here
   if (slot < 0 || slot >= p.size_limit) {
@@ -133,20 +174,16 @@ __global__ void __launch_bounds__(kStoreWarps* kWarp) store_kv_kernel(const Stor
                           (long long)p.size_limit);
     __trap();
   }
-  const bool is_v = seg >= p.k_segs;
-  const int s = is_v ? seg - p.k_segs : seg;
-  const int row_elems = is_v ? p.v_row_elems : p.k_row_elems;
-  const SRC* src = reinterpret_cast<const SRC*>(is_v ? p.v : p.k) +
-                   token * (is_v ? p.v_src_stride : p.k_src_stride) + (int64_t)s * kSegElems;
-  DST* dst = reinterpret_cast<DST*>(is_v ? p.v_cache : p.k_cache) +
-             slot * (is_v ? p.v_cache_stride : p.k_cache_stride) + (int64_t)s * kSegElems;
-  const float scale = is_v ? p.v_scale : p.k_scale;
-  const bool scaled = scale != 1.0f;
-  const int remaining = row_elems - s * kSegElems;
+  DST* k_dst = reinterpret_cast<DST*>(p.k_cache) + slot * p.k_cache_stride + (int64_t)s * kSegElems;
+  DST* v_dst = reinterpret_cast<DST*>(p.v_cache) + slot * p.v_cache_stride + (int64_t)s * kSegElems;
   if constexpr (kVecOK) {
-    if (lane * kVec < remaining) move_vec8<SRC, DST>(src + lane * kVec, dst + lane * kVec, scale, scaled);
+    if (k_on) finish_vec8<SRC, DST>(k_raw, k_dst + lane * kVec, p.k_scale, p.k_scale != 1.0f);
+    if (v_on) finish_vec8<SRC, DST>(v_raw, v_dst + lane * kVec, p.v_scale, p.v_scale != 1.0f);
   } else {
-    move_scalar<SRC, DST>(src, dst, remaining < kSegElems ? remaining : kSegElems, lane, scale, scaled);
+    if (k_rem > 0)
+      move_scalar<SRC, DST>(k_src, k_dst, k_rem < kSegElems ? k_rem : kSegElems, lane, p.k_scale, p.k_scale != 1.0f);
+    if (v_rem > 0)
+      move_scalar<SRC, DST>(v_src, v_dst, v_rem < kSegElems ? v_rem : kSegElems, lane, p.v_scale, p.v_scale != 1.0f);
   }
 }
 
@@ -159,7 +196,8 @@ int launch_store(const b200_store_kv_args& a, cudaStream_t stream) {
   p.num_tokens = a.num_tokens; p.size_limit = a.size_limit; p.skip_index = a.skip_index;
   p.k_row_elems = a.k_row_elems; p.v_row_elems = a.v_row_elems;
   p.k_segs = (a.k_row_elems + kSegElems - 1) / kSegElems;
-  p.segs = p.k_segs + (a.v_row_elems + kSegElems - 1) / kSegElems;
+  const int v_segs = (a.v_row_elems + kSegElems - 1) / kSegElems;
+  p.segs = p.k_segs > v_segs ? p.k_segs : v_segs;          // warps per token: one per 256-element segment
   p.k_scale = a.k_scale; p.v_scale = a.v_scale; p.loc_is_i64 = a.loc_is_i64;
   const int64_t warps = a.num_tokens * p.segs;
   const int64_t blocks = (warps + kStoreWarps - 1) / kStoreWarps;
