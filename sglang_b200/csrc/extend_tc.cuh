@@ -30,7 +30,6 @@ namespace tc {
 
 constexpr int kD = 128;            // head dim of this instance
 constexpr int kBlockKV = 128;      // kv tokens per MMA block
-constexpr int kSlots = 5;          // ring slots, one K or V block each
 constexpr int kQTiles = 2;
 constexpr int kSoftmaxWarps = 4;                     // per query tile
 constexpr int kMmaWarp = 8;
@@ -44,27 +43,35 @@ constexpr int kQTileBytes = 128 * kRowBytes;         // 32 KiB: two 128-row x 12
 constexpr int kSlotBytes = kBlockKV * kRowBytes;     // 32 KiB: two 128-row x 128-byte blocks
 constexpr int kHalfBytes = kBlockKV * 128;           // distance between the two 64-wide d halves of a tile
 
-constexpr int kSmemQ = 0;
-constexpr int kSmemKV = kSmemQ + kQTiles * kQTileBytes;
-constexpr int kSmemBar = kSmemKV + kSlots * kSlotBytes;
-constexpr int kSmemBytes = kSmemBar + 256 + 1024;    // barriers + slack for the 1024-byte alignment
+constexpr int kRawBytes = kBlockKV * kD;             // one FP8 K or V block as it sits in the pool (16 KiB)
 
 constexpr int kTmemCols = 512;
 constexpr int kTmemS = 0, kTmemO = 256;
 
 constexpr int kRegsSoftmax = 200, kRegsOther = 56;   // 256 x 200 + 256 x 56 = 64 Ki registers
 
-// barrier slots (8 bytes each)
-enum {
-  kBarQFull = 0,
-  kBarFull = 1,                      // kSlots
-  kBarEmpty = kBarFull + kSlots,     // kSlots
-  kBarSFull = kBarEmpty + kSlots,    // kQTiles each below
-  kBarPFull = kBarSFull + kQTiles,
-  kBarODone = kBarPFull + kQTiles,
-  kNumBars = kBarODone + kQTiles,
+// Shared-memory map and barrier slots.  16-bit pools: 5 ring slots.  FP8 pools: 4 ring slots (the MMA
+// operands are f16 tiles the producers write) + 2 raw 16 KiB landing buffers for the cp.async gathers.
+template <bool kFp8>
+struct Layout {
+  static constexpr int kSlots = kFp8 ? 4 : 5;          // ring slots, one K or V block each
+  static constexpr int kRawBufs = kFp8 ? 2 : 0;
+  static constexpr int kSmemQ = 0;
+  static constexpr int kSmemKV = kSmemQ + kQTiles * kQTileBytes;
+  static constexpr int kSmemRaw = kSmemKV + kSlots * kSlotBytes;
+  static constexpr int kSmemBar = kSmemRaw + kRawBufs * kRawBytes;
+  static constexpr int kSmemBytes = kSmemBar + 256 + 1024;    // barriers + slack for the 1024-byte alignment
+  // barrier slots (8 bytes each)
+  static constexpr int kBarQFull = 0;
+  static constexpr int kBarFull = 1;                     // kSlots
+  static constexpr int kBarEmpty = kBarFull + kSlots;    // kSlots
+  static constexpr int kBarSFull = kBarEmpty + kSlots;   // kQTiles each below
+  static constexpr int kBarPFull = kBarSFull + kQTiles;
+  static constexpr int kBarODone = kBarPFull + kQTiles;
+  static constexpr int kNumBars = kBarODone + kQTiles;
+  static_assert(kNumBars * 8 + 8 <= 256, "barrier area");
+  static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
-static_assert(kNumBars * 8 + 8 <= 256, "barrier area");
 
 // byte offset of (row, 16-byte chunk) inside a tile made of 128-byte-wide swizzle blocks of `rows` rows
 __device__ __forceinline__ uint32_t swz_off(int row, int chunk, int rows) {
@@ -74,10 +81,19 @@ __device__ __forceinline__ uint32_t swz_off(int row, int chunk, int rows) {
 }  // namespace tc
 
 // kEmu: how many of every 8 column pairs take the polynomial exp2 (FMA pipe) instead of MUFU.EX2.
-template <typename QT, int kEmu>
+// kFp8: the pool holds FP8-e4m3 bytes; the MMAs then run in f16 (e4m3 -> f16 is exact) on tiles the producers
+// dequantise, Q is converted to f16 on its way into shared memory and P is packed as f16.
+template <typename QT, int kEmu, bool kFp8>
 __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const ExtendParams p, const int max_tiles) {
   using namespace tc;
   using namespace ptx;
+  using L = Layout<kFp8>;
+  using CT = typename std::conditional<kFp8, __half, QT>::type;   // MMA operand type
+  constexpr int kSlots = L::kSlots, kSmemQ = L::kSmemQ, kSmemKV = L::kSmemKV, kSmemRaw = L::kSmemRaw,
+                kSmemBar = L::kSmemBar, kNumBars = L::kNumBars;
+  constexpr int kBarQFull = L::kBarQFull, kBarFull = L::kBarFull, kBarEmpty = L::kBarEmpty,
+                kBarSFull = L::kBarSFull, kBarPFull = L::kBarPFull, kBarODone = L::kBarODone;
+  (void)kSmemRaw;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -124,7 +140,11 @@ __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const Extend
 
   if (warp >= kProducerWarp0) {
     setmaxnreg_dec<kRegsOther>();
+    if constexpr (kFp8) {
+#include "extend_tc_producer_fp8.inc"
+    } else {
 #include "extend_tc_producer.inc"
+    }
   } else if (warp >= kMmaWarp) {
     setmaxnreg_dec<kRegsOther>();
     if (warp == kMmaWarp) {
@@ -147,27 +167,29 @@ bool extend_fast_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype
   if (dqk != tc::kD || dv != tc::kD) return false;
   if (group < 1 || group > 128) return false;
   if (q_dtype != B200_BF16 && q_dtype != B200_F16) return false;
-  return kv_dtype == q_dtype;   // FP8 pools take the generic kernel until the dequantising producer lands
+  return kv_dtype == q_dtype || kv_dtype == B200_FP8_E4M3;
 }
 
 // query tokens per work item (two 128-row tiles of 128/group tokens each)
 int extend_fast_block_q(int group) { return tc::kQTiles * (128 / group); }
 
 bool extend_fast_layout_ok(const ExtendParams& p, int kv_dtype) {
-  (void)kv_dtype;
+  const int kv_align = kv_dtype == B200_FP8_E4M3 ? 16 : 8;     // pool rows are read in 16-byte pieces
   auto a16 = [](const void* ptr) { return ((uintptr_t)ptr & 15) == 0; };
-  return a16(p.k_cache) && a16(p.v_cache) && a16(p.q) && a16(p.o) && p.k_stride_s % 8 == 0 &&
-         p.k_stride_h % 8 == 0 && p.v_stride_s % 8 == 0 && p.v_stride_h % 8 == 0 && p.q_stride_t % 8 == 0 &&
+  return a16(p.k_cache) && a16(p.v_cache) && a16(p.q) && a16(p.o) && p.k_stride_s % kv_align == 0 &&
+         p.k_stride_h % kv_align == 0 && p.v_stride_s % kv_align == 0 && p.v_stride_h % kv_align == 0 &&
+         p.q_stride_t % 8 == 0 &&
          p.q_stride_h % 8 == 0 && p.o_stride_t % 8 == 0 && p.o_stride_h % 8 == 0 &&
          p.k_stride_s > 0 && p.v_stride_s > 0 && p.k_stride_s < (1ll << 30) && p.v_stride_s < (1ll << 30);
 }
 
-template <typename QT, int kEmu>
+template <typename QT, int kEmu, bool kFp8>
 int launch_extend_fast_t(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   static bool configured = false;
-  auto kern = extend_tc_kernel<QT, kEmu>;
+  constexpr int kSmem = tc::Layout<kFp8>::kSmemBytes;
+  auto kern = extend_tc_kernel<QT, kEmu, kFp8>;
   if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmemBytes));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     configured = true;
   }
   const int block_q = extend_fast_block_q(p.group);
@@ -176,7 +198,7 @@ int launch_extend_fast_t(const ExtendParams& p, const b200_extend_args& a, cudaS
   if (tiles > a.max_tiles) tiles = a.max_tiles;
   const int64_t grid = tiles * p.num_kv_heads;
   B200_CHECK_ARG(grid > 0 && grid < 0x7fffffff, "extend: bad grid %lld", (long long)grid);
-  kern<<<(unsigned)grid, tc::kThreads, tc::kSmemBytes, stream>>>(p, (int)tiles);
+  kern<<<(unsigned)grid, tc::kThreads, kSmem, stream>>>(p, (int)tiles);
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;
 }
@@ -188,28 +210,27 @@ int extend_emu_eighths() {
   if (v < 0) {
     const char* e = getenv("B200ATTN_EXTEND_EMU");
     v = e ? atoi(e) : 3;
-    if (v < 0 || v > 8) v = 3;
+    if (v < 0 || v > 3) v = 3;
   }
   return v;
 }
 
-template <typename QT>
+template <typename QT, bool kFp8>
 int launch_extend_fast_q(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   switch (extend_emu_eighths()) {
-    case 0: return launch_extend_fast_t<QT, 0>(p, a, stream);
-    case 1: return launch_extend_fast_t<QT, 1>(p, a, stream);
-    case 2: return launch_extend_fast_t<QT, 2>(p, a, stream);
-    case 4: return launch_extend_fast_t<QT, 4>(p, a, stream);
-    case 5: return launch_extend_fast_t<QT, 5>(p, a, stream);
-    case 6: return launch_extend_fast_t<QT, 6>(p, a, stream);
-    case 8: return launch_extend_fast_t<QT, 8>(p, a, stream);
-    default: return launch_extend_fast_t<QT, 3>(p, a, stream);
+    case 0: return launch_extend_fast_t<QT, 0, kFp8>(p, a, stream);
+    case 1: return launch_extend_fast_t<QT, 1, kFp8>(p, a, stream);
+    case 2: return launch_extend_fast_t<QT, 2, kFp8>(p, a, stream);
+    default: return launch_extend_fast_t<QT, 3, kFp8>(p, a, stream);
   }
 }
 
 int launch_extend_fast(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
-  if (a.q_dtype == B200_BF16) return launch_extend_fast_q<__nv_bfloat16>(p, a, stream);
-  return launch_extend_fast_q<__half>(p, a, stream);
+  const bool fp8 = a.kv_dtype == B200_FP8_E4M3;
+  if (a.q_dtype == B200_BF16)
+    return fp8 ? launch_extend_fast_q<__nv_bfloat16, true>(p, a, stream)
+               : launch_extend_fast_q<__nv_bfloat16, false>(p, a, stream);
+  return fp8 ? launch_extend_fast_q<__half, true>(p, a, stream) : launch_extend_fast_q<__half, false>(p, a, stream);
 }
 
 }  // namespace
