@@ -147,6 +147,31 @@ def store_case(name, T, Hkv, D, pool_dtype, iters):
     return dict(case=name, kind="store", us=round(t * 1e6, 2), gbs=round(gbs, 1), frac_measured=round(gbs / HBM, 3))
 
 
+def rope_store_case(name, T, Hq, Hkv, D, pool_dtype, iters):
+    """Fused rotary + KV store vs the bytes it must move: q r/w, k r/w, v read, pool write."""
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(0)
+    rows = max(T * 2, 1 << 18) + 1
+    q = torch.randn(T, Hq * D, generator=g, device=dev, dtype=torch.bfloat16)
+    k = torch.randn(T, Hkv * D, generator=g, device=dev, dtype=torch.bfloat16)
+    v = torch.randn(T, Hkv * D, generator=g, device=dev, dtype=torch.bfloat16)
+    es = 1 if pool_dtype == torch.float8_e4m3fn else 2
+    kc = torch.zeros(rows, Hkv, D, device=dev, dtype=torch.uint8 if es == 1 else torch.bfloat16)
+    vc = torch.zeros_like(kc)
+    loc = torch.randperm(rows - 1, generator=g, device=dev)[:T] + 1
+    pos = torch.randint(0, 32768, (T,), generator=g, device=dev)
+    inv = 1.0 / (500000.0 ** (torch.arange(0, D, 2, device=dev).float() / D))
+    fr = torch.arange(32768, device=dev).float()[:, None] * inv[None]
+    cache = torch.cat((fr.cos(), fr.sin()), dim=-1).contiguous()
+    fn = lambda: ops.rope_store_kv(pos, q, k, v, cache, D, k_cache=kc, v_cache=vc, loc=loc, cache_dtype=pool_dtype)  # noqa: E731
+    t = time_cuda(fn, iters)
+    if t < 80e-6:
+        t = time_cuda_graph(fn)
+    nbytes = T * (Hq * D * 4 + Hkv * D * (4 + es) + Hkv * D * (2 + es) + 16)
+    gbs = nbytes / t / 1e9
+    return dict(case=name, kind="rope+store", us=round(t * 1e6, 2), gbs=round(gbs, 1), frac_measured=round(gbs / HBM, 3))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default="")
@@ -176,6 +201,10 @@ def main():
         emit(store_case("decode store 256 rows 8B fp8", 256, 8, 128, e4, a.iters))
         emit(store_case("cfg5 store 131072 rows 8B bf16", 131072, 8, 128, bf, a.iters))
         emit(store_case("cfg5 store 131072 rows 8B fp8", 131072, 8, 128, e4, a.iters))
+    if a.only in ("", "store", "rope"):
+        emit(rope_store_case("decode rope+store 64 rows 8B bf16", 64, 32, 8, 128, bf, a.iters))
+        emit(rope_store_case("cfg5 rope+store 131072 rows 8B bf16", 131072, 32, 8, 128, bf, a.iters))
+        emit(rope_store_case("cfg5 rope+store 131072 rows 8B fp8", 131072, 32, 8, 128, e4, a.iters))
     if a.only in ("", "extend"):
         it = max(3, a.iters // 10)
         emit(extend_case("cfg5/16 8 req x (16K shared prefix + 1K)", 8, 16384, 1024, 32, 8, 128, it))

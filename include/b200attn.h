@@ -21,6 +21,7 @@
  *                            kernels/ops/attention/decode_attention.py:968-1044 (decode_attention_fwd:
  *                            split-KV stage 1 + stage-2 merge)
  *   b200attn_extend_plan     srt/layers/attention/triton_backend.py:860-900 (qo_indptr / kv_indptr for extend)
+ *   b200attn_rope_store_kv   srt/layers/rotary_embedding/base.py:234-275,363-385 + set_kv_buffer (see below)
  *   b200attn_extend          srt/layers/attention/torch_native_backend.py:61-174 (oracle semantics),
  *                            kernels/ops/attention/extend_attention.py:664-812 (extend_attention_fwd)
  */
@@ -241,6 +242,62 @@ int b200attn_extend_fast_supported(int32_t head_dim_qk, int32_t head_dim_v, int3
 /* query tokens per tile the kernel that would be picked uses (for the plan) */
 int b200attn_extend_block_q(int32_t head_dim_qk, int32_t head_dim_v, int32_t group,
                             int32_t q_dtype, int32_t kv_dtype, int32_t kernel);
+
+/* ------------------------------------------------------------------------ *
+ * Fused rotary embedding + KV-store (the step right before RadixAttention.forward).
+ * Stands in for  q, k = rotary_emb(positions, q, k)  followed by  set_kv_buffer(layer, loc, k, v):
+ *   srt/layers/rotary_embedding/base.py:234-275 (forward_native) / :363-385 (forward_cuda with
+ *   fused_set_kv_buffer_arg), srt/layers/rotary_embedding/utils.py:36-60 (apply_rotary_emb),
+ *   kernels/ops/kvcache/rope_cache.py:99-545 (fused_qk_rope_reshape_and_cache), srt/models/llama.py:219-223.
+ * One launch: reads q, k, v once; writes the rotated q in place, the rotated k in place (write_k != 0)
+ * and k_cache[loc] / v_cache[loc] with the cast / scale / skip rules of b200attn_store_kv.
+ *   cos_sin_cache[pos] = cos(pos * inv_freq[0..rot/2)) | sin(...)   (rotary_dim values per position)
+ *   neox:  pairs (i, i + rot/2);  gpt-j: pairs (2i, 2i + 1);  elements >= rotary_dim pass through.
+ *   rounding = B200_ROPE_FP32:   o = round(x1*cos - x2*sin) computed in fp32, one rounding (what the
+ *                                reference's CUDA kernel does with its fp32 cache)
+ *   rounding = B200_ROPE_NATIVE: cos/sin rounded to the model dtype, every product and the sum rounded to
+ *                                the model dtype -- bit-exact with forward_native / apply_rotary_emb
+ * ------------------------------------------------------------------------ */
+enum { B200_ROPE_FP32 = 0, B200_ROPE_NATIVE = 1 };
+enum { B200_CACHE_F32 = 0, B200_CACHE_MODEL_DTYPE = 1 };
+
+typedef struct b200_rope_store_args {
+  void* q;                   /* [num_tokens, num_q_heads, head_dim] src_dtype, rotated in place */
+  void* k;                   /* [num_tokens, num_kv_heads, head_dim] */
+  const void* v;             /* [num_tokens, num_kv_heads, v_head_dim] */
+  int64_t q_stride_t;        /* elements between tokens; heads are contiguous (stride head_dim) */
+  int64_t k_stride_t;
+  int64_t v_stride_t;
+  const void* positions;     /* [num_tokens] int32 or int64 */
+  int32_t positions_is_i64;
+  const void* cos_sin_cache; /* [max_position, rotary_dim] */
+  int32_t cache_dtype;       /* B200_CACHE_F32 or B200_CACHE_MODEL_DTYPE (same as src_dtype) */
+  int64_t max_position;      /* positions outside [0, max_position) trap */
+  int32_t rotary_dim;        /* even, <= head_dim */
+  int32_t head_dim;
+  int32_t v_head_dim;
+  int32_t num_q_heads;
+  int32_t num_kv_heads;
+  int32_t is_neox;
+  int32_t rounding;          /* B200_ROPE_* */
+  int32_t write_k;           /* also write the rotated k back to `k` */
+  /* store part: same meaning as in b200_store_kv_args; k_cache == NULL skips the store */
+  void* k_cache;
+  void* v_cache;
+  int64_t k_cache_stride;
+  int64_t v_cache_stride;
+  const void* loc;
+  int32_t loc_is_i64;
+  int64_t num_tokens;
+  int32_t src_dtype;         /* B200_BF16 or B200_F16 */
+  int32_t dst_dtype;         /* pool dtype */
+  float k_scale;
+  float v_scale;
+  int64_t size_limit;
+  int64_t skip_index;
+} b200_rope_store_args;
+
+int b200attn_rope_store_kv(const b200_rope_store_args* args, b200_stream_t stream);
 
 #ifdef __cplusplus
 }

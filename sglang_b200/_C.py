@@ -29,6 +29,22 @@ class StoreKVArgs(C.Structure):
     ]
 
 
+class RopeStoreArgs(C.Structure):
+    _fields_ = [
+        ("q", vp), ("k", vp), ("v", vp), ("q_stride_t", i64), ("k_stride_t", i64), ("v_stride_t", i64),
+        ("positions", vp), ("positions_is_i64", i32), ("cos_sin_cache", vp), ("cache_dtype", i32),
+        ("max_position", i64), ("rotary_dim", i32), ("head_dim", i32), ("v_head_dim", i32),
+        ("num_q_heads", i32), ("num_kv_heads", i32), ("is_neox", i32), ("rounding", i32), ("write_k", i32),
+        ("k_cache", vp), ("v_cache", vp), ("k_cache_stride", i64), ("v_cache_stride", i64),
+        ("loc", vp), ("loc_is_i64", i32), ("num_tokens", i64), ("src_dtype", i32), ("dst_dtype", i32),
+        ("k_scale", f32), ("v_scale", f32), ("size_limit", i64), ("skip_index", i64),
+    ]
+
+
+ROPE_FP32, ROPE_NATIVE = 0, 1
+CACHE_F32, CACHE_MODEL_DTYPE = 0, 1
+
+
 class DecodePlanArgs(C.Structure):
     _fields_ = [
         ("seq_lens", vp), ("seq_lens_is_i64", i32), ("batch_size", i32), ("max_bs", i32),
@@ -87,6 +103,7 @@ SYMBOLS = {
     "b200attn_device_info": (C.c_int, [C.POINTER(C.c_int)] * 3),
     "b200attn_store_kv": (C.c_int, [C.POINTER(StoreKVArgs), vp]),
     "b200attn_decode_plan_ints": (i64, [i32, i32]),
+    "b200attn_rope_store_kv": (C.c_int, [C.POINTER(RopeStoreArgs), vp]),
     "b200attn_decode_plan": (C.c_int, [C.POINTER(DecodePlanArgs), vp]),
     "b200attn_decode": (C.c_int, [C.POINTER(DecodeArgs), vp]),
     "b200attn_decode_fast_supported": (C.c_int, [i32] * 5),

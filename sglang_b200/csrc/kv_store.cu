@@ -217,6 +217,8 @@ int launch_store(const b200_store_kv_args& a, cudaStream_t stream) {
   return B200_OK;
 }
 
+#include "rope_store.cuh"
+
 }  // namespace
 }  // namespace b200
 
@@ -240,5 +242,53 @@ extern "C" int b200attn_store_kv(const b200_store_kv_args* a, b200_stream_t stre
   if (s == B200_BF16 && d == B200_FP8_E5M2) return launch_store<__nv_bfloat16, e5m2_t>(*a, stream);
   if (s == B200_F16 && d == B200_FP8_E5M2) return launch_store<__half, e5m2_t>(*a, stream);
   set_error("store_kv: unsupported dtype pair src=%d dst=%d", s, d);
+  return B200_EINVAL;
+}
+
+extern "C" int b200attn_rope_store_kv(const b200_rope_store_args* a, b200_stream_t stream_) {
+  using namespace b200;
+  B200_CHECK_ARG(a != nullptr, "rope_store_kv: null args");
+  if (a->num_tokens == 0) return B200_OK;
+  B200_CHECK_ARG(a->q && a->k && a->positions && a->cos_sin_cache, "rope_store_kv: null pointer");
+  B200_CHECK_ARG(a->k_cache == nullptr || (a->v && a->v_cache && a->loc), "rope_store_kv: null v / v_cache / loc");
+  B200_CHECK_ARG(a->num_tokens > 0 && a->num_q_heads > 0 && a->num_kv_heads > 0, "rope_store_kv: bad sizes");
+  B200_CHECK_ARG(a->src_dtype == B200_BF16 || a->src_dtype == B200_F16, "rope_store_kv: src dtype %d", a->src_dtype);
+  B200_CHECK_ARG(a->k_scale > 0.f && a->v_scale > 0.f, "rope_store_kv: scales must be positive");
+  const int D = a->head_dim, Dv = a->v_head_dim, rot = a->rotary_dim;
+  B200_CHECK_ARG(D > 0 && D % kVec == 0 && Dv > 0 && Dv % kVec == 0, "rope_store_kv: head dims must be multiples of 8");
+  B200_CHECK_ARG(rot > 0 && rot <= D && rot % (a->is_neox ? 2 * kVec : kVec) == 0,
+                 "rope_store_kv: rotary_dim %d must be a multiple of %d and <= head_dim", rot,
+                 a->is_neox ? 2 * kVec : kVec);
+  auto a16 = [](const void* ptr) { return ((uintptr_t)ptr & 15) == 0; };
+  B200_CHECK_ARG(a16(a->q) && a16(a->k) && a16(a->v) && a->q_stride_t % kVec == 0 && a->k_stride_t % kVec == 0 &&
+                     a->v_stride_t % kVec == 0 && a->k_cache_stride % 16 == 0 && a->v_cache_stride % 16 == 0 &&
+                     a16(a->k_cache) && a16(a->v_cache),
+                 "rope_store_kv: pointers must be 16-byte aligned and strides multiples of 8 (16 for the pool)");
+  RopeParams p;
+  p.q = a->q; p.k = a->k; p.v = a->v;
+  p.q_stride_t = a->q_stride_t; p.k_stride_t = a->k_stride_t; p.v_stride_t = a->v_stride_t;
+  p.positions = a->positions; p.cache = a->cos_sin_cache; p.max_position = a->max_position;
+  p.k_cache = a->k_cache; p.v_cache = a->v_cache;
+  p.k_cache_stride = a->k_cache_stride; p.v_cache_stride = a->v_cache_stride;
+  p.loc = a->loc; p.num_tokens = a->num_tokens; p.size_limit = a->size_limit; p.skip_index = a->skip_index;
+  p.positions_is_i64 = a->positions_is_i64; p.loc_is_i64 = a->loc_is_i64;
+  p.cache_is_f32 = a->cache_dtype == B200_CACHE_F32;
+  p.rot = rot; p.D = D; p.Dv = Dv; p.Hq = a->num_q_heads; p.Hkv = a->num_kv_heads;
+  p.is_neox = a->is_neox; p.native = a->rounding == B200_ROPE_NATIVE; p.write_k = a->write_k;
+  const int n_rot_units = a->is_neox ? rot / (2 * kVec) : rot / kVec;
+  p.uq = p.uk = n_rot_units + (D - rot) / kVec;
+  p.uv = a->k_cache ? Dv / kVec : 0;
+  const int hpt = rope_heads_per_thread(p.Hq, p.Hkv);
+  p.units_per_token = (p.Hq / hpt) * p.uq + (p.Hkv / hpt) * p.uk + p.Hkv * p.uv;   // threads per token
+  p.k_scale = a->k_scale; p.v_scale = a->v_scale;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  const int s = a->src_dtype, d = a->k_cache ? a->dst_dtype : a->src_dtype;
+  if (s == B200_BF16 && d == B200_BF16) return launch_rope_store<__nv_bfloat16, __nv_bfloat16>(p, stream);
+  if (s == B200_F16 && d == B200_F16) return launch_rope_store<__half, __half>(p, stream);
+  if (s == B200_BF16 && d == B200_FP8_E4M3) return launch_rope_store<__nv_bfloat16, e4m3_t>(p, stream);
+  if (s == B200_F16 && d == B200_FP8_E4M3) return launch_rope_store<__half, e4m3_t>(p, stream);
+  if (s == B200_BF16 && d == B200_FP8_E5M2) return launch_rope_store<__nv_bfloat16, e5m2_t>(p, stream);
+  if (s == B200_F16 && d == B200_FP8_E5M2) return launch_rope_store<__half, e5m2_t>(p, stream);
+  set_error("rope_store_kv: unsupported dtype pair src=%d dst=%d", s, d);
   return B200_EINVAL;
 }

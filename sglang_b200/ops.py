@@ -120,6 +120,82 @@ def store_kv(
     launch_count += 1
 
 
+def rope_store_kv(
+    positions: torch.Tensor,       # [T] int32 / int64
+    q: torch.Tensor,               # [T, Hq * D] or [T, Hq, D], rotated in place
+    k: torch.Tensor,               # [T, Hkv * D] or [T, Hkv, D], rotated in place when write_k
+    v: Optional[torch.Tensor],     # [T, Hkv * Dv] or [T, Hkv, Dv]
+    cos_sin_cache: torch.Tensor,   # [max_position, rotary_dim] float32 or the model dtype
+    head_dim: int,
+    *,
+    is_neox: bool = True,
+    k_cache: Optional[torch.Tensor] = None,   # [slots, Hkv, D]; None = rotate only
+    v_cache: Optional[torch.Tensor] = None,
+    loc: Optional[torch.Tensor] = None,
+    cache_dtype: Optional[torch.dtype] = None,
+    k_scale: Optional[float] = None,
+    v_scale: Optional[float] = None,
+    native_rounding: bool = False,
+    write_k: bool = True,
+    skip_index: int = 0,
+) -> None:
+    """Fused `rotary_emb(positions, q, k)` + `set_kv_buffer(layer, loc, k, v)` in one launch.
+
+    Mirrors RotaryEmbedding.forward_cuda with `fused_set_kv_buffer_arg` (reference
+    srt/layers/rotary_embedding/base.py:363-385) followed by the cast/scale rules of
+    `MHATokenToKVPool.set_kv_buffer`.  `native_rounding=True` reproduces `forward_native`
+    (every product and sum rounded to the model dtype) bit for bit; the default computes each output
+    in fp32 with one rounding, like the reference's CUDA kernel."""
+    global launch_count
+    T = positions.shape[0]
+    if T == 0:
+        return
+    _need_cuda(positions, q, k, cos_sin_cache)
+    q3, k3 = q.view(T, -1, head_dim), k.view(T, -1, head_dim)
+    if q3.stride(2) != 1 or k3.stride(2) != 1 or q3.stride(1) != head_dim or k3.stride(1) != head_dim:
+        raise ValueError("q / k heads must be contiguous ([T, H, D] with strides (*, D, 1))")
+    if cos_sin_cache.dim() != 2 or not cos_sin_cache.is_contiguous():
+        raise ValueError("cos_sin_cache must be a contiguous [max_position, rotary_dim] tensor")
+    if cos_sin_cache.dtype == torch.float32:
+        cdt = _C.CACHE_F32
+    elif cos_sin_cache.dtype == q.dtype:
+        cdt = _C.CACHE_MODEL_DTYPE
+    else:
+        raise ValueError(f"cos_sin_cache must be float32 or {q.dtype}, got {cos_sin_cache.dtype}")
+    Hq, Hkv = q3.shape[1], k3.shape[1]
+    a = _C.RopeStoreArgs(
+        q=q3.data_ptr(), k=k3.data_ptr(), q_stride_t=q3.stride(0), k_stride_t=k3.stride(0),
+        positions=positions.data_ptr(), positions_is_i64=_index_kind(positions, "positions"),
+        cos_sin_cache=cos_sin_cache.data_ptr(), cache_dtype=cdt, max_position=cos_sin_cache.shape[0],
+        rotary_dim=cos_sin_cache.shape[1], head_dim=head_dim, v_head_dim=head_dim,
+        num_q_heads=Hq, num_kv_heads=Hkv, is_neox=1 if is_neox else 0,
+        rounding=_C.ROPE_NATIVE if native_rounding else _C.ROPE_FP32, write_k=1 if write_k else 0,
+        num_tokens=T, src_dtype=dtype_code(q.dtype), dst_dtype=dtype_code(q.dtype),
+        k_scale=1.0 if k_scale is None else float(k_scale), v_scale=1.0 if v_scale is None else float(v_scale),
+        size_limit=0, skip_index=skip_index,
+    )
+    if k_cache is not None:
+        if v is None or v_cache is None or loc is None:
+            raise ValueError("k_cache needs v, v_cache and loc as well")
+        _need_cuda(v, k_cache, v_cache, loc)
+        kc, vc = k_cache.view(k_cache.shape[0], -1), v_cache.view(v_cache.shape[0], -1)
+        v3 = v.view(T, Hkv, -1)
+        if v3.stride(2) != 1 or v3.stride(1) != v3.shape[2]:
+            raise ValueError("v heads must be contiguous")
+        if kc.shape[1] != Hkv * head_dim or vc.shape[1] != Hkv * v3.shape[2]:
+            raise ValueError(f"row width mismatch: k/v {Hkv}x{head_dim}/{v3.shape[2]} vs cache {tuple(kc.shape)}")
+        if loc.dim() != 1 or loc.shape[0] != T or loc.stride(0) != 1:
+            raise ValueError("loc must be a contiguous 1-D tensor with one slot id per token")
+        a.v, a.v_stride_t, a.v_head_dim = v3.data_ptr(), v3.stride(0), v3.shape[2]
+        a.k_cache, a.v_cache = kc.data_ptr(), vc.data_ptr()
+        a.k_cache_stride, a.v_cache_stride = kc.stride(0), vc.stride(0)
+        a.loc, a.loc_is_i64 = loc.data_ptr(), _index_kind(loc, "loc")
+        a.dst_dtype = dtype_code(cache_dtype or k_cache.dtype)
+        a.size_limit = kc.shape[0]
+    _C.check(_C.lib.b200attn_rope_store_kv(C.byref(a), _stream()), "rope_store_kv")
+    launch_count += 1
+
+
 # --------------------------------------------------------------------------- decode
 @dataclass
 class DecodeWorkspace:

@@ -98,3 +98,35 @@ def test_attention_oracle_matches_reference(name):
     # the reference as it runs in production (model dtype, SDPA internals): dtype-rounding tolerance
     want = c.out_ref.float().view(T, c.Hq, c.D)
     assert float((out - want).abs().max()) <= 2e-2
+
+
+# ----------------------------------------------------------------------------- rotary embedding
+def _rope_names():
+    return [str(n) for n in np.load(GOLDEN / "rope.npz")["names"]]
+
+
+@pytest.mark.parametrize("name", _rope_names())
+def test_rope_oracle_matches_reference_bit_exact(name):
+    """oracle/rope_ref (native rounding) == the reference's apply_rotary_emb run on CPU (oracle/gen_golden_rope.py)."""
+    from oracle import rope_ref
+
+    z = np.load(GOLDEN / "rope.npz")
+    dt_i, neox, T, Hq, Hkv, D, rot = (int(x) for x in z[f"{name}.meta"])
+    dt = torch.bfloat16 if dt_i == 0 else torch.float16
+    q = from_bits(z[f"{name}.q"], dt).view(T, Hq * D)
+    k = from_bits(z[f"{name}.k"], dt).view(T, Hkv * D)
+    cache = torch.from_numpy(z[f"{name}.cache_rows_f32"].copy())
+    q2, k2 = rope_ref.rope_ref(torch.arange(T), q, k, cache, D, bool(neox), native_rounding=True)
+    assert torch.equal(q2.view(torch.int16), from_bits(z[f"{name}.q_out"], dt).view(T, Hq * D).view(torch.int16))
+    assert torch.equal(k2.view(torch.int16), from_bits(z[f"{name}.k_out"], dt).view(T, Hkv * D).view(torch.int16))
+    # the float32 evaluation of the same formula differs only by the op-by-op roundings (|x| <= ~12 here)
+    q3, _ = rope_ref.rope_ref(torch.arange(T), q, k, cache, D, bool(neox), native_rounding=False)
+    assert torch.allclose(q3.float(), q2.float(), rtol=0, atol=0.13 if dt_i == 0 else 0.02)
+
+
+def test_rope_cache_formula():
+    from oracle import rope_ref
+
+    c = rope_ref.cos_sin_cache(64, 32, 10000.0)
+    assert c.shape == (32, 64) and torch.all(c[0, :32] == 1) and torch.all(c[0, 32:] == 0)
+    assert abs(float(c[1, 0]) - np.cos(1.0)) < 1e-6 and abs(float(c[3, 32]) - np.sin(3.0)) < 1e-6
