@@ -24,6 +24,7 @@
  *   b200attn_rope_store_kv   srt/layers/rotary_embedding/base.py:234-275,363-385 + set_kv_buffer (see below)
  *   b200attn_extend          srt/layers/attention/torch_native_backend.py:61-174 (oracle semantics),
  *                            kernels/ops/attention/extend_attention.py:664-812 (extend_attention_fwd)
+ *   b200attn_merge_state     kernels/aot/csrc/attention/merge_attn_states.cu, kernels/ops/attention/merge_state.py
  */
 #ifndef B200ATTN_H_
 #define B200ATTN_H_
@@ -34,7 +35,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 1
+#define B200ATTN_ABI_VERSION 2
 
 typedef void* b200_stream_t; /* a cudaStream_t */
 
@@ -124,6 +125,9 @@ typedef struct b200_decode_plan_args {
                                 per-item overhead estimate (in tokens) when it ranks candidate chunk sizes */
   int32_t fixed_chunk_tokens;/* > 0 overrides the heuristic (deterministic splits) */
   int32_t* plan;             /* device, b200attn_decode_plan_ints() ints */
+  int32_t window_keys;       /* sliding window: only the last window_keys tokens of a request are attended
+                                (0 = off).  torch_native's sliding_window_size W is window_keys = W + 1
+                                (torch_native_backend.py:36-48: k_pos >= q_pos - W) */
 } b200_decode_plan_args;
 
 int b200attn_decode_plan(const b200_decode_plan_args* args, b200_stream_t stream);
@@ -163,6 +167,11 @@ typedef struct b200_decode_args {
   int32_t kernel;            /* B200_KERNEL_* */
   void* ev_attn_start;       /* optional cudaEvent_t recorded right before the attention kernel */
   void* ev_attn_stop;        /* optional cudaEvent_t recorded right after it (before a separate merge) */
+  int32_t window_keys;       /* sliding window, same value the plan was built with (0 = off) */
+  const float* sinks;        /* optional [Hq] fp32 attention-sink logits (natural-log units, not scaled):
+                                denominator += exp(sink_h - max)  (extend_attention.py:633-635,
+                                decode_attention.py stage 2); NULL = none */
+  float* lse;                /* optional [bs, Hq] natural-log LSE output (sink included), NULL = none */
 } b200_decode_args;
 
 int b200attn_decode(const b200_decode_args* args, b200_stream_t stream);
@@ -234,6 +243,14 @@ typedef struct b200_extend_args {
   int32_t kernel;
   float* lse;                /* optional [sum E_r, Hq] natural-log LSE output, may be NULL */
   int64_t pool_slots;        /* rows in k_cache / v_cache (bounds the TMA descriptors) */
+  int32_t window_keys;       /* sliding window: query at position x attends kv positions (x - window_keys, x]
+                                (0 = off; extend_attention.py:391-398 with SLIDING_WINDOW_SIZE = window_keys - 1) */
+  const float* sinks;        /* optional [Hq] fp32 attention-sink logits, NULL = none */
+  const uint8_t* custom_mask;   /* optional tree / speculative mask (extend_attention.py:378-390,525-539): request r,
+                                   query i, kv position x is visible iff custom_mask[mask_indptr[r] + i * (P_r + E_r) + x]
+                                   != 0.  Replaces the causal rule on the new tokens (x >= P_r); NULL = none */
+  const int64_t* mask_indptr;   /* [bs + 1] offsets into custom_mask */
+  int32_t mask_skip_prefix;     /* 1: prefix positions (x < P_r) are always visible (SKIP_PREFIX_CUSTOM_MASK) */
 } b200_extend_args;
 
 int b200attn_extend(const b200_extend_args* args, b200_stream_t stream);
@@ -298,6 +315,29 @@ typedef struct b200_rope_store_args {
 } b200_rope_store_args;
 
 int b200attn_rope_store_kv(const b200_rope_store_args* args, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------ *
+ * Merge two partial attention states (chunked prefix / cascade):
+ *   lse = log(exp(lse_a) + exp(lse_b));  o = o_a * exp(lse_a - lse) + o_b * exp(lse_b - lse)
+ * Stands in for merge_state_v2 (kernels/aot/csrc/attention/merge_attn_states.cu:60-70) and the Triton
+ * merge_state_kernel (kernels/ops/attention/merge_state.py:9-66): an LSE of +inf is treated as -inf
+ * (empty state).
+ * ------------------------------------------------------------------------ */
+typedef struct b200_merge_state_args {
+  const void* o_a;           /* [T, H, D] dtype */
+  const float* lse_a;        /* [T, H] natural log */
+  const void* o_b;
+  const float* lse_b;
+  void* o;                   /* [T, H, D] dtype (may alias o_a or o_b) */
+  float* lse;                /* optional [T, H] */
+  int64_t num_tokens;
+  int32_t num_heads;
+  int32_t head_dim;          /* multiple of 8 */
+  int32_t dtype;             /* B200_BF16 / B200_F16 */
+  int64_t oa_stride_t, oa_stride_h, ob_stride_t, ob_stride_h, o_stride_t, o_stride_h;  /* elements */
+} b200_merge_state_args;
+
+int b200attn_merge_state(const b200_merge_state_args* args, b200_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -14,7 +14,7 @@ LIB_PATH = Path(os.environ.get("B200ATTN_LIB", _PKG_DIR / "lib" / "libb200attn.s
 
 B200_BF16, B200_F16, B200_FP8_E4M3, B200_FP8_E5M2 = 0, 1, 2, 3
 KERNEL_AUTO, KERNEL_GENERIC, KERNEL_FAST = 0, 1, 2
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 i32, i64, f32, vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
@@ -49,7 +49,7 @@ class DecodePlanArgs(C.Structure):
     _fields_ = [
         ("seq_lens", vp), ("seq_lens_is_i64", i32), ("batch_size", i32), ("max_bs", i32),
         ("max_chunks", i32), ("num_kv_heads", i32), ("num_ctas", i32), ("waves", i32),
-        ("min_chunk_tokens", i32), ("fixed_chunk_tokens", i32), ("plan", vp),
+        ("min_chunk_tokens", i32), ("fixed_chunk_tokens", i32), ("plan", vp), ("window_keys", i32),
     ]
 
 
@@ -68,6 +68,7 @@ class DecodeArgs(C.Structure):
         ("plan", vp), ("max_bs", i32), ("max_chunks", i32),
         ("ws_o", vp), ("ws_lse", vp), ("num_ctas", i32), ("kernel", i32),
         ("ev_attn_start", vp), ("ev_attn_stop", vp),
+        ("window_keys", i32), ("sinks", vp), ("lse", vp),
     ]
 
 
@@ -93,6 +94,16 @@ class ExtendArgs(C.Structure):
         ("sm_scale", f32), ("k_scale", f32), ("v_scale", f32), ("logit_cap", f32),
         ("causal", i32), ("plan", vp), ("max_bs", i32), ("max_tiles", i32),
         ("num_ctas", i32), ("kernel", i32), ("lse", vp), ("pool_slots", i64),
+        ("window_keys", i32), ("sinks", vp), ("custom_mask", vp), ("mask_indptr", vp), ("mask_skip_prefix", i32),
+    ]
+
+
+class MergeStateArgs(C.Structure):
+    _fields_ = [
+        ("o_a", vp), ("lse_a", vp), ("o_b", vp), ("lse_b", vp), ("o", vp), ("lse", vp),
+        ("num_tokens", i64), ("num_heads", i32), ("head_dim", i32), ("dtype", i32),
+        ("oa_stride_t", i64), ("oa_stride_h", i64), ("ob_stride_t", i64), ("ob_stride_h", i64),
+        ("o_stride_t", i64), ("o_stride_h", i64),
     ]
 
 
@@ -114,6 +125,7 @@ SYMBOLS = {
     "b200attn_extend": (C.c_int, [C.POINTER(ExtendArgs), vp]),
     "b200attn_extend_fast_supported": (C.c_int, [i32] * 5),
     "b200attn_extend_block_q": (C.c_int, [i32] * 6),
+    "b200attn_merge_state": (C.c_int, [C.POINTER(MergeStateArgs), vp]),
 }
 
 

@@ -69,8 +69,15 @@ class B200AttnBackend(_Base):
         self.v_head_dim = pool.v_buffer[0].shape[-1]
         self.kv_dtype = pool.dtype
         self._q_dtype = getattr(model_runner, "dtype", torch.bfloat16)
-        if getattr(model_runner, "sliding_window_size", None) not in (None, -1):
-            raise NotImplementedError("b200 backend: sliding-window layers are not supported yet")
+        # Sliding-window layers (hybrid SWA models): layer.sliding_window_size = W means the query at position x
+        # attends positions [x - W, x] -- W + 1 keys, the rule of torch_native_backend.py:36-48 and of the Triton
+        # extend kernel (extend_attention.py:391-398).  The Triton *decode* metadata clamps to min(seq_len, W) keys
+        # instead (triton_backend.py:686-691); this backend follows the torch_native oracle in both modes.
+        sw = getattr(model_runner, "sliding_window_size", None)
+        self.sliding_window_size = int(sw) if sw is not None and sw > -1 else None
+        if hasattr(pool, "translate_loc_from_full_to_swa"):
+            raise NotImplementedError("b200 backend: the separate SWA KV pool (SWAKVPool) is not supported; "
+                                      "sliding-window layers read the full pool")
 
         self.max_bs = int(self.req_to_token_pool.size)
         self.max_context_len = int(getattr(cfg, "context_len", self.req_to_token_pool.max_context_len))
@@ -81,11 +88,33 @@ class B200AttnBackend(_Base):
                                                         self.v_head_dim, self._q_dtype, self.kv_dtype)
         self.decode_ws = ops.DecodeWorkspace.create(
             self.max_bs, self.num_head, self.v_head_dim, dev, num_ctas=self.decode_ctas, waves=self.DECODE_WAVES)
+        # second split-KV plan for the sliding-window layers (same partial buffers: layers run one after another)
+        self.decode_ws_swa = self._swa_workspace(self.decode_ws)
+        self._verify_ext: Optional[torch.Tensor] = None
+        self._mask_indptr: Optional[torch.Tensor] = None
         self.extend_ws: Optional[ops.ExtendWorkspace] = None
         self._extend_block_q = 64
         self.forward_metadata = None
         #: optional (start, stop) torch.cuda.Event pair re-recorded around the next decode attention kernel
         self.attn_events = None
+
+    def _swa_workspace(self, ws):
+        if self.sliding_window_size is None:
+            return None
+        return ops.DecodeWorkspace(max_bs=ws.max_bs, max_chunks=ws.max_chunks, num_ctas=ws.num_ctas,
+                                   plan=torch.zeros_like(ws.plan), ws_o=ws.ws_o, ws_lse=ws.ws_lse)
+
+    def _window_keys(self, layer) -> int:
+        sw = getattr(layer, "sliding_window_size", -1)
+        return int(sw) + 1 if sw is not None and sw > -1 else 0
+
+    @staticmethod
+    def _draft_token_num(forward_batch) -> int:
+        spec = getattr(forward_batch, "spec_info", None)
+        n = getattr(spec, "draft_token_num", None)
+        if n is None:
+            raise ValueError("TARGET_VERIFY needs forward_batch.spec_info.draft_token_num")
+        return int(n)
 
     # ------------------------------------------------------------------ metadata
     def init_forward_metadata_out_graph(self, forward_batch, in_capture: bool = False):
@@ -98,9 +127,18 @@ class B200AttnBackend(_Base):
             if forward_batch.batch_size > self.max_bs:
                 raise ValueError(f"batch size {forward_batch.batch_size} exceeds pool size {self.max_bs}")
             return
-        T = int(forward_batch.extend_num_tokens if forward_batch.extend_num_tokens is not None
-                else forward_batch.out_cache_loc.shape[0])
         bs = int(forward_batch.batch_size)
+        if mode.is_target_verify():
+            # every request extends by draft_token_num tokens over a prefix of seq_lens tokens
+            # (triton_backend.py:807-866); the per-request lengths live in static buffers
+            T = bs * self._draft_token_num(forward_batch)
+            if self._verify_ext is None or self._verify_ext.shape[0] < bs:
+                n = max(self.max_bs, bs)
+                self._verify_ext = torch.zeros(n, dtype=forward_batch.seq_lens.dtype, device=self.device)
+                self._mask_indptr = torch.zeros(n + 1, dtype=torch.int64, device=self.device)
+        else:
+            T = int(forward_batch.extend_num_tokens if forward_batch.extend_num_tokens is not None
+                    else forward_batch.out_cache_loc.shape[0])
         group = self.num_head // self.num_kv_head
         q_dtype = self._q_dtype_hint
         self._extend_block_q = ops.extend_block_q(self.head_dim, self.v_head_dim, group, q_dtype,
@@ -118,8 +156,19 @@ class B200AttnBackend(_Base):
         if mode.is_idle():
             return
         if mode.is_decode():
-            ops.decode_plan(self.decode_ws, forward_batch.seq_lens[: forward_batch.batch_size],
-                            self.num_kv_head, waves=self.DECODE_WAVES, items_per_chunk=self._decode_items)
+            seq_lens = forward_batch.seq_lens[: forward_batch.batch_size]
+            ops.decode_plan(self.decode_ws, seq_lens, self.num_kv_head, waves=self.DECODE_WAVES,
+                            items_per_chunk=self._decode_items)
+            if self.decode_ws_swa is not None:
+                ops.decode_plan(self.decode_ws_swa, seq_lens, self.num_kv_head, waves=self.DECODE_WAVES,
+                                items_per_chunk=self._decode_items, window_keys=self.sliding_window_size + 1)
+        elif mode.is_target_verify():
+            bs, n = forward_batch.batch_size, self._draft_token_num(forward_batch)
+            ext = self._verify_ext[:bs]
+            ext.fill_(n)
+            pre = forward_batch.seq_lens[:bs]
+            torch.cumsum((pre.to(torch.int64) + n) * n, dim=0, out=self._mask_indptr[1 : bs + 1])
+            ops.extend_plan(self.extend_ws, ext, self._extend_block_q)
         else:
             ops.extend_plan(self.extend_ws, forward_batch.extend_seq_lens, self._extend_block_q)
 
@@ -137,6 +186,7 @@ class B200AttnBackend(_Base):
         self.decode_ws = ops.DecodeWorkspace.create(
                 max_bs, self.num_head, self.v_head_dim, self.device, num_ctas=self.decode_ctas,
                 waves=self.DECODE_WAVES)
+        self.decode_ws_swa = self._swa_workspace(self.decode_ws)
 
     def get_cuda_graph_seq_len_fill_value(self):
         return 1
@@ -157,13 +207,31 @@ class B200AttnBackend(_Base):
             size_limit=pool.size + pool.page_size, skip_index=0,
         )
 
-    @staticmethod
-    def _check_layer(layer):
+    def _check_layer(self, layer):
         if getattr(layer, "is_cross_attention", False):
             raise NotImplementedError("b200 backend: cross attention is not supported")
-        sw = getattr(layer, "sliding_window_size", -1)
-        if sw is not None and sw > -1:
-            raise NotImplementedError("b200 backend: sliding-window layers are not supported yet")
+        if int(getattr(layer, "xai_temperature_len", -1) or -1) > 0:
+            raise NotImplementedError("b200 backend: xai_temperature_len is not supported")
+        wk = self._window_keys(layer)
+        if wk and (self.sliding_window_size is None or wk != self.sliding_window_size + 1):
+            raise ValueError(f"b200 backend: layer window {wk - 1} differs from the model runner's "
+                             f"sliding_window_size {self.sliding_window_size}")
+
+    @staticmethod
+    def _logit_cap(layer) -> float:
+        # logit_capping_mod (reference srt/layers/attention/triton_backend.py:83-88): tanh is the only method
+        method = getattr(layer, "logit_capping_method", "tanh") or "tanh"
+        cap = float(getattr(layer, "logit_cap", 0.0) or 0.0)
+        if cap > 0.0 and method != "tanh":
+            raise NotImplementedError(f"b200 backend: logit capping method {method!r} is not supported")
+        return cap
+
+    @staticmethod
+    def _sinks(kwargs, device):
+        sinks = kwargs.get("sinks")
+        if sinks is None:
+            return None
+        return sinks.to(device=device, dtype=torch.float32).contiguous()
 
     def _descale(self, layer):
         if getattr(layer, "k_scale", None) is not None and getattr(layer, "v_scale", None) is not None:
@@ -178,8 +246,6 @@ class B200AttnBackend(_Base):
     # ------------------------------------------------------------------ forward
     def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):
         self._check_layer(layer)
-        if kwargs.get("sinks") is not None:
-            raise NotImplementedError("b200 backend: attention sinks are not supported")
         q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
         if layer.qk_head_dim != layer.v_head_dim:
             o = q.new_empty((q.shape[0], layer.tp_q_head_num * layer.v_head_dim))
@@ -190,23 +256,27 @@ class B200AttnBackend(_Base):
         k_buf, v_buf = self._pool_buffers(layer)
         k_descale, v_descale = self._descale(layer)
         bs = q.shape[0]
+        window_keys = self._window_keys(layer)
         ops.decode_attention(
             q.view(bs, layer.tp_q_head_num, layer.qk_head_dim),
             o.view(bs, layer.tp_q_head_num, layer.v_head_dim),
             k_buf, v_buf,
             self.req_to_token_pool.req_to_token,
             forward_batch.req_pool_indices[:bs], forward_batch.seq_lens[:bs],
-            self.decode_ws, layer.scaling,
+            self.decode_ws_swa if window_keys else self.decode_ws, layer.scaling,
             kv_dtype=self.kv_dtype, k_scale=k_descale, v_scale=v_descale,
-            logit_cap=float(getattr(layer, "logit_cap", 0.0) or 0.0), kernel=self.decode_kernel,
-            attn_events=self.attn_events,
+            logit_cap=self._logit_cap(layer), kernel=self.decode_kernel,
+            attn_events=self.attn_events, window_keys=window_keys, sinks=self._sinks(kwargs, q.device),
         )
         return o
 
     def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):
+        """EXTEND / MIXED / DRAFT_EXTEND: prefix + causal new tokens.  TARGET_VERIFY: every request extends by
+        `spec_info.draft_token_num` tokens over `seq_lens` cached ones under `spec_info.custom_mask` (the tree
+        mask replaces the causal rule on the new tokens, triton_backend.py:807-866).  With
+        `forward_batch.mha_return_lse` the call returns `(o [T, Hq, Dv], lse [T, Hq])`
+        (radix_attention.py:244-277)."""
         self._check_layer(layer)
-        if kwargs.get("sinks") is not None:
-            raise NotImplementedError("b200 backend: attention sinks are not supported")
         attn_out = getattr(forward_batch, "_attn_output", None)
         if attn_out is not None:
             o = attn_out
@@ -223,17 +293,32 @@ class B200AttnBackend(_Base):
         attn_type = getattr(layer, "attn_type", None)
         causal = not (getattr(attn_type, "value", attn_type) == _AT.ENCODER_ONLY.value)
         T = q.shape[0]
+        prefix_lens, extend_lens = forward_batch.extend_prefix_lens, forward_batch.extend_seq_lens
+        custom_mask = mask_indptr = None
+        if forward_batch.forward_mode.is_target_verify():
+            bs = forward_batch.batch_size
+            prefix_lens, extend_lens = forward_batch.seq_lens[:bs], self._verify_ext[:bs]
+            custom_mask = getattr(forward_batch.spec_info, "custom_mask", None)
+            if custom_mask is not None:
+                mask_indptr = self._mask_indptr[: bs + 1]
+        lse = None
+        if getattr(forward_batch, "mha_return_lse", False):
+            lse = torch.empty((T, layer.tp_q_head_num), dtype=torch.float32, device=q.device)
         ops.extend_attention(
             q.view(T, layer.tp_q_head_num, layer.qk_head_dim),
             o.view(T, layer.tp_q_head_num, layer.v_head_dim),
             k_buf, v_buf,
             self.req_to_token_pool.req_to_token,
-            forward_batch.req_pool_indices, forward_batch.extend_prefix_lens, forward_batch.extend_seq_lens,
+            forward_batch.req_pool_indices, prefix_lens, extend_lens,
             self.extend_ws, layer.scaling,
             kv_dtype=self.kv_dtype, k_scale=k_descale, v_scale=v_descale,
-            logit_cap=float(getattr(layer, "logit_cap", 0.0) or 0.0), causal=causal,
-            kernel=self.extend_kernel,
+            logit_cap=self._logit_cap(layer), causal=causal,
+            kernel=self.extend_kernel, lse=lse,
+            window_keys=self._window_keys(layer) if causal else 0, sinks=self._sinks(kwargs, q.device),
+            custom_mask=custom_mask, mask_indptr=mask_indptr, mask_skip_prefix=True,
         )
+        if lse is not None:
+            return o.view(T, layer.tp_q_head_num, layer.v_head_dim), lse
         return o
 
     def support_triton(self):

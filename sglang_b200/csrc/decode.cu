@@ -30,7 +30,14 @@ struct PlanParams {
   int32_t* plan;
   int32_t seq_lens_is_i64, batch_size, max_bs, max_chunks;
   int32_t num_kv_heads, num_ctas, waves, min_chunk, fixed_chunk;
+  int32_t window_keys;   // sliding window: only the last window_keys tokens of a request are attended (0 = off)
 };
+
+// tokens of a request that are attended: all of them, or the last `window_keys`
+__device__ __forceinline__ int64_t attended_len(const void* seq_lens, int is_i64, int r, int window_keys) {
+  const int64_t L = load_index(seq_lens, is_i64, r);
+  return (window_keys > 0 && L > window_keys) ? (int64_t)window_keys : L;
+}
 
 constexpr int kPlanThreads = 1024;
 
@@ -62,7 +69,7 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanPar
 
   int64_t local = 0;
   for (int r = tid; r < bs; r += kPlanThreads) {
-    const int64_t L = load_index(p.seq_lens, p.seq_lens_is_i64, r);
+    const int64_t L = attended_len(p.seq_lens, p.seq_lens_is_i64, r, p.window_keys);
     local += L > 0 ? L : 0;
   }
   const int64_t total = block_sum_i64(local, s_red);
@@ -75,7 +82,7 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanPar
     const int m = warp + 1;
     int64_t maxl = 0;
     for (int r = lane; r < bs; r += 32) {
-      const int64_t L = load_index(p.seq_lens, p.seq_lens_is_i64, r);
+      const int64_t L = attended_len(p.seq_lens, p.seq_lens_is_i64, r, p.window_keys);
       maxl = L > maxl ? L : maxl;
     }
 #pragma unroll
@@ -86,7 +93,7 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanPar
     auto items = [&](int64_t chunk) -> int64_t {
       int64_t n = 0;
       for (int r = lane; r < bs; r += 32) {
-        const int64_t L = load_index(p.seq_lens, p.seq_lens_is_i64, r);
+        const int64_t L = attended_len(p.seq_lens, p.seq_lens_is_i64, r, p.window_keys);
         if (L > 0) n += (L + chunk - 1) / chunk;
       }
 #pragma unroll
@@ -136,7 +143,7 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanPar
     const int r = base + tid;
     int32_t n = 0;
     if (r < bs) {
-      const int64_t L = load_index(p.seq_lens, p.seq_lens_is_i64, r);
+      const int64_t L = attended_len(p.seq_lens, p.seq_lens_is_i64, r, p.window_keys);
       n = L > 0 ? (int32_t)((L + chunk - 1) / chunk) : 0;
     }
     int32_t inc = n;
@@ -172,6 +179,7 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanPar
     p.plan[1] = total_chunks;
     p.plan[2] = bs;
     p.plan[3] = p.max_chunks;
+    p.plan[4] = p.window_keys;
   }
   __syncthreads();
   // owner of each chunk: binary search in chunk_offset (block-visible after the barrier)
@@ -206,8 +214,16 @@ struct DecodeParams {
   int32_t batch_size, num_q_heads, num_kv_heads, group;
   int32_t head_dim_qk, head_dim_v;
   int32_t max_bs;
+  int32_t window_keys;
   float sm_scale, k_scale, v_scale, logit_cap;
+  const float* sinks;   // [Hq] natural-log sink logits or nullptr
+  float* lse;           // [bs, Hq] natural-log LSE output or nullptr
 };
+
+// attention-sink logit of q head h in log2 units (-inf when there are no sinks)
+__device__ __forceinline__ float sink_log2(const DecodeParams& p, int h) {
+  return p.sinks != nullptr ? p.sinks[h] * kLog2e : -INFINITY;
+}
 
 struct ChunkInfo {
   int req;        // batch row
@@ -225,13 +241,15 @@ __device__ __forceinline__ ChunkInfo load_chunk(const DecodeParams& p, int c) {
   ci.req = chunk_req[c];
   const int off = chunk_offset[ci.req];
   ci.n_chunks = chunk_offset[ci.req + 1] - off;
-  const int64_t L = load_index(p.seq_lens, p.seq_lens_is_i64, ci.req);
+  const int64_t L_full = load_index(p.seq_lens, p.seq_lens_is_i64, ci.req);
+  const int64_t L = (p.window_keys > 0 && L_full > p.window_keys) ? (int64_t)p.window_keys : L_full;
   // equal-sized chunks inside a request: n = ceil(L / chunk) pieces of roundup16(ceil(L / n)) tokens
   // (16 = the kernels' token tile; cs <= chunk because chunk is a multiple of 16, so (n-1) cs < L)
   const int cs = (int)(((L + ci.n_chunks - 1) / ci.n_chunks + 15) / 16 * 16);
-  ci.start = (c - off) * cs;
-  const int64_t rem = L - ci.start;
+  const int rel = (c - off) * cs;                       // first token of the chunk inside the attended range
+  const int64_t rem = L - rel;
   ci.n_tok = (int)(rem < cs ? rem : cs);
+  ci.start = (int)(L_full - L) + rel;                   // the attended range is the last L tokens of the request
   (void)chunk;
   ci.pool_row = load_index(p.req_pool_indices, p.req_pool_indices_is_i64, ci.req);
   return ci;
@@ -272,15 +290,18 @@ __global__ void __launch_bounds__(kGenWarps* kWarp) decode_generic_kernel(const 
     attend_row_generic<KVT>(st, q_s, pt, ci.n_tok, kc, vc, p.k_stride_s, p.v_stride_s,
                             (int64_t)kvh * p.k_stride_h, (int64_t)kvh * p.v_stride_h, Dk, Dv, qk_scale,
                             p.logit_cap);
-    const float inv_l = 1.f / st.l;
     if (ci.n_chunks == 1) {
+      const float l_fin = st.l + exp2f(sink_log2(p, h) - st.m);   // + the attention sink's share of the denominator
+      const float inv_l = p.v_scale / l_fin;
       QT* orow = reinterpret_cast<QT*>(p.o) + (int64_t)ci.req * p.o_stride_t + (int64_t)h * p.o_stride_h;
 #pragma unroll
       for (int i = 0; i < kGenAcc; ++i) {
         const int d = lane + i * kWarp;
-        if (d < Dv) orow[d] = from_float<QT>(st.acc[i] * inv_l * p.v_scale);
+        if (d < Dv) orow[d] = from_float<QT>(st.acc[i] * inv_l);
       }
+      if (p.lse != nullptr && lane == 0) p.lse[(int64_t)ci.req * Hq + h] = (st.m + log2f(l_fin)) * kLn2;
     } else {
+      const float inv_l = 1.f / st.l;
       float* wo = p.ws_o + ((int64_t)c * Hq + h) * Dv;
 #pragma unroll
       for (int i = 0; i < kGenAcc; ++i) {
@@ -311,6 +332,7 @@ __global__ void __launch_bounds__(kMergeWarps* kWarp) decode_merge_kernel(const 
   QT* orow = reinterpret_cast<QT*>(p.o) + (int64_t)r * p.o_stride_t + (int64_t)h * p.o_stride_h;
   if (n == 0) {
     for (int d = lane; d < Dv; d += kWarp) orow[d] = from_float<QT>(0.f);
+    if (p.lse != nullptr && lane == 0) p.lse[(int64_t)r * Hq + h] = -INFINITY;
     return;
   }
   float mx = -INFINITY;
@@ -318,7 +340,8 @@ __global__ void __launch_bounds__(kMergeWarps* kWarp) decode_merge_kernel(const 
   mx = warp_max(mx);
   float den = 0.f;
   for (int i = lane; i < n; i += kWarp) den += exp2f(p.ws_lse[(int64_t)(c0 + i) * Hq + h] - mx);
-  den = warp_sum(den);
+  den = warp_sum(den) + exp2f(sink_log2(p, h) - mx);
+  if (p.lse != nullptr && lane == 0) p.lse[(int64_t)r * Hq + h] = (mx + log2f(den)) * kLn2;
   const float inv = p.v_scale / den;
   for (int d0 = 0; d0 < Dv; d0 += kWarp) {
     const int d = d0 + lane;
@@ -378,6 +401,7 @@ extern "C" int b200attn_decode_plan(const b200_decode_plan_args* a, b200_stream_
   p.batch_size = a->batch_size; p.max_bs = a->max_bs; p.max_chunks = a->max_chunks;
   p.num_kv_heads = a->num_kv_heads; p.num_ctas = a->num_ctas; p.waves = a->waves;
   p.min_chunk = a->min_chunk_tokens; p.fixed_chunk = a->fixed_chunk_tokens;
+  p.window_keys = a->window_keys > 0 ? a->window_keys : 0;
   decode_plan_kernel<<<1, kPlanThreads, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(p);
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;
@@ -452,13 +476,14 @@ extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_)
   p.group = a->num_q_heads / a->num_kv_heads;
   p.head_dim_qk = a->head_dim_qk; p.head_dim_v = a->head_dim_v; p.max_bs = a->max_bs;
   p.sm_scale = a->sm_scale; p.k_scale = a->k_scale; p.v_scale = a->v_scale; p.logit_cap = a->logit_cap;
+  p.window_keys = a->window_keys > 0 ? a->window_keys : 0; p.sinks = a->sinks; p.lse = a->lse;
 
   const bool fast_ok = decode_fast_supported(a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype) &&
                        decode_fast_layout_ok(p, a->kv_dtype);
   B200_CHECK_ARG(!(a->kernel == B200_KERNEL_FAST && !fast_ok),
                  "decode: fast kernel does not cover Dk=%d Dv=%d group=%d q=%d kv=%d (or unaligned strides)",
                  a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype);
-  const bool use_fast = fast_ok && a->kernel != B200_KERNEL_GENERIC && a->logit_cap == 0.f;
+  const bool use_fast = fast_ok && a->kernel != B200_KERNEL_GENERIC;
   int rc;
   if (a->ev_attn_start) B200_CHECK_CUDA(cudaEventRecord(reinterpret_cast<cudaEvent_t>(a->ev_attn_start), stream));
   const bool use_hg = use_fast && decode_hg_enabled() && decode_hg_supported(p, a->q_dtype, a->kv_dtype);

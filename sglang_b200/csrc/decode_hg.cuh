@@ -58,6 +58,8 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
   const int n_groups = Hkv / kHG;
   const int n_items = total_chunks * n_groups;
   const float scale_log2 = p.sm_scale * p.k_scale * kLog2e;
+  const bool capped = p.logit_cap > 0.f;               // s = cap * tanh(s * sm_scale / cap)
+  const float cap_in = capped ? p.sm_scale * p.k_scale / p.logit_cap : 0.f, cap_out = p.logit_cap * kLog2e;
   const int64_t k_slot_b = p.k_stride_s * C::kEsz, v_slot_b = p.v_stride_s * C::kEsz;
   uint32_t n_issue = 0, n_cons = 0;   // tiles issued / consumed by this warp since kernel start (ring phases)
 
@@ -195,7 +197,7 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const int tok = tok0 + 8 * nt + (e & 1);
-          float v = s_acc[nt][e] * scale_log2;
+          float v = capped ? cap_out * tanh_ex2(s_acc[nt][e] * cap_in) : s_acc[nt][e] * scale_log2;
           if (tok >= n_tok) v = -INFINITY;
           s_acc[nt][e] = v;
           if (UPPER || e < 2) pmax[e >> 1] = fmaxf(pmax[e >> 1], v);
@@ -286,6 +288,11 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
       const int row = qrow + 8 * half;
       if (row < g) {
         const int h = kvh * g + row;
+        if (final_out) {                                   // attention sink + LSE of single-chunk requests
+          l_run[half] += exp2f(sink_log2(p, h) - m_run[half]);
+          if (p.lse != nullptr && quad == 0)
+            p.lse[(int64_t)ci.req * Hq + h] = (m_run[half] + log2f(l_run[half])) * kLn2;
+        }
         const float inv = (final_out ? p.v_scale : 1.f) / l_run[half];
         QT* orow = reinterpret_cast<QT*>(p.o) + (int64_t)ci.req * p.o_stride_t + (int64_t)h * p.o_stride_h;
         float* wrow = p.ws_o + ((int64_t)c * Hq + h) * D;

@@ -129,6 +129,8 @@ __global__ void __launch_bounds__(kFastWarps* kWarp) decode_merge_fast_kernel(co
   float dsum = 0.f;
 #pragma unroll
   for (int w = 0; w < kFastWarps; ++w) dsum += s_ml[w][0];
+  dsum += exp2f(sink_log2(p, h) - m);                  // attention sink: only the denominator grows
+  if (p.lse != nullptr && threadIdx.x == 0) p.lse[(int64_t)req * Hq + h] = (m + log2f(dsum)) * kLn2;
   const float inv = p.v_scale / dsum;
   QT* orow = reinterpret_cast<QT*>(p.o) + (int64_t)req * p.o_stride_t + (int64_t)h * p.o_stride_h;
   for (int d = threadIdx.x; d < D; d += kFastWarps * kWarp) {
@@ -155,6 +157,8 @@ __global__ void __launch_bounds__(kFastWarps* kWarp, (FastCfg<D, KV>::kCtaSmem >
   const int Hkv = p.num_kv_heads, g = p.group, Hq = p.num_q_heads;
   const int n_items = total_chunks * Hkv;
   const float scale_log2 = p.sm_scale * p.k_scale * kLog2e;
+  const bool capped = p.logit_cap > 0.f;               // s = cap * tanh(s * sm_scale / cap)
+  const float cap_in = capped ? p.sm_scale * p.k_scale / p.logit_cap : 0.f, cap_out = p.logit_cap * kLog2e;
   const uint8_t* kc = reinterpret_cast<const uint8_t*>(p.k_cache);
   const uint8_t* vc = reinterpret_cast<const uint8_t*>(p.v_cache);
   const int64_t k_slot_b = p.k_stride_s * C::kEsz, v_slot_b = p.v_stride_s * C::kEsz;
@@ -293,7 +297,7 @@ __global__ void __launch_bounds__(kFastWarps* kWarp, (FastCfg<D, KV>::kCtaSmem >
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const int tok = tok0 + 8 * nt + (e & 1);
-          float v = s_acc[nt][e] * scale_log2;
+          float v = capped ? cap_out * tanh_ex2(s_acc[nt][e] * cap_in) : s_acc[nt][e] * scale_log2;
           if (tok >= w_ntok) v = -INFINITY;
           s_acc[nt][e] = v;
           if (UPPER || e < 2) pmax[e >> 1] = fmaxf(pmax[e >> 1], v);
@@ -412,11 +416,13 @@ __global__ void __launch_bounds__(kFastWarps* kWarp, (FastCfg<D, KV>::kCtaSmem >
         den = fmaf(wgt, ow[16 * D + 16 + row], den);
       }
       const int h = kvh * g + row;
-      const float val = num / den;
       if (final_out) {
+        const float den_fin = den + exp2f(sink_log2(p, h) - M);
         reinterpret_cast<QT*>(p.o)[(int64_t)ci.req * p.o_stride_t + (int64_t)h * p.o_stride_h + d] =
-            from_float<QT>(val * p.v_scale);
+            from_float<QT>(num / den_fin * p.v_scale);
+        if (p.lse != nullptr && d == 0) p.lse[(int64_t)ci.req * Hq + h] = (M + log2f(den_fin)) * kLn2;
       } else {
+        const float val = num / den;
         p.ws_o[((int64_t)c * Hq + h) * D + d] = val;
         if (d == 0) p.ws_lse[(int64_t)c * Hq + h] = M + log2f(den);
       }

@@ -114,7 +114,12 @@ struct ExtendParams {
   int32_t batch_size, num_q_heads, num_kv_heads, group;
   int32_t head_dim_qk, head_dim_v;
   int32_t max_bs, causal;
+  int32_t window_keys;          // query at position x attends (x - window_keys, x]; 0 = off
+  int32_t mask_skip_prefix;
   float sm_scale, k_scale, v_scale, logit_cap;
+  const float* sinks;           // [Hq] natural-log sink logits or nullptr
+  const uint8_t* custom_mask;   // see b200_extend_args
+  const int64_t* mask_indptr;
 };
 
 // ----------------------------------------------------------------------------
@@ -146,7 +151,12 @@ __global__ void __launch_bounds__(kGenWarps* kWarp) extend_generic_kernel(const 
     const int r = lo, i = t - qo_indptr[r];
     const int64_t P = load_index(p.extend_prefix_lens, p.lens_is_i64, r);
     const int64_t E = load_index(p.extend_seq_lens, p.lens_is_i64, r);
-    const int kv_len = (int)(p.causal ? P + i + 1 : P + E);
+    const bool masked = p.custom_mask != nullptr;      // the custom mask replaces the causal rule on the new tokens
+    const int kv_len = (int)((p.causal && !masked) ? P + i + 1 : P + E);
+    int kv_lo = 0;                                     // sliding window: positions (x - window_keys, x], x = P + i
+    if (p.window_keys > 0 && P + i + 1 > p.window_keys) kv_lo = (int)(P + i + 1 - p.window_keys);
+    const uint8_t* mrow = masked ? p.custom_mask + p.mask_indptr[r] + (int64_t)i * (P + E) + kv_lo : nullptr;
+    const int mask_from = p.mask_skip_prefix ? (int)P - kv_lo : 0;
     const int64_t pool_row = load_index(p.req_pool_indices, p.req_pool_indices_is_i64, r);
     const int kvh = h / p.group;
     const QT* qrow = q + (int64_t)t * p.q_stride_t + (int64_t)h * p.q_stride_h;
@@ -156,9 +166,10 @@ __global__ void __launch_bounds__(kGenWarps* kWarp) extend_generic_kernel(const 
     RowState st;
 #pragma unroll
     for (int j = 0; j < kGenAcc; ++j) st.acc[j] = 0.f;
-    attend_row_generic<KVT>(st, q_s, p.req_to_token + pool_row * p.req_to_token_stride, kv_len, kc, vc,
-                            p.k_stride_s, p.v_stride_s, (int64_t)kvh * p.k_stride_h,
-                            (int64_t)kvh * p.v_stride_h, Dk, Dv, qk_scale, p.logit_cap);
+    attend_row_generic<KVT>(st, q_s, p.req_to_token + pool_row * p.req_to_token_stride + kv_lo, kv_len - kv_lo,
+                            kc, vc, p.k_stride_s, p.v_stride_s, (int64_t)kvh * p.k_stride_h,
+                            (int64_t)kvh * p.v_stride_h, Dk, Dv, qk_scale, p.logit_cap, mrow, mask_from);
+    if (p.sinks != nullptr) st.l += exp2f(p.sinks[h] * kLog2e - st.m);   // sink: denominator only
     const float inv_l = st.l > 0.f ? p.v_scale / st.l : 0.f;
     QT* orow = reinterpret_cast<QT*>(p.o) + (int64_t)t * p.o_stride_t + (int64_t)h * p.o_stride_h;
 #pragma unroll
@@ -252,13 +263,19 @@ extern "C" int b200attn_extend(const b200_extend_args* a, b200_stream_t stream_)
   p.group = a->num_q_heads / a->num_kv_heads;
   p.head_dim_qk = a->head_dim_qk; p.head_dim_v = a->head_dim_v; p.max_bs = a->max_bs; p.causal = a->causal;
   p.sm_scale = a->sm_scale; p.k_scale = a->k_scale; p.v_scale = a->v_scale; p.logit_cap = a->logit_cap;
+  p.window_keys = a->window_keys > 0 ? a->window_keys : 0; p.sinks = a->sinks;
+  p.custom_mask = a->custom_mask; p.mask_indptr = a->mask_indptr; p.mask_skip_prefix = a->mask_skip_prefix;
+  B200_CHECK_ARG(a->custom_mask == nullptr || a->mask_indptr != nullptr, "extend: custom_mask needs mask_indptr");
+  B200_CHECK_ARG(!(p.window_keys > 0 && !a->causal), "extend: a sliding window needs causal attention");
 
   const bool fast_ok = extend_fast_supported(a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype) &&
                        extend_fast_layout_ok(p, a->kv_dtype);
   B200_CHECK_ARG(!(a->kernel == B200_KERNEL_FAST && !fast_ok),
                  "extend: fast kernel does not cover Dk=%d Dv=%d group=%d q=%d kv=%d (or unaligned strides)",
                  a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype);
-  const bool use_fast = fast_ok && a->kernel != B200_KERNEL_GENERIC && a->logit_cap == 0.f;
+  B200_CHECK_ARG(!(a->kernel == B200_KERNEL_FAST && a->custom_mask != nullptr),
+                 "extend: custom masks run on the generic kernel only");
+  const bool use_fast = fast_ok && a->kernel != B200_KERNEL_GENERIC && a->custom_mask == nullptr;
   if (use_fast) return launch_extend_fast(p, *a, stream);
   if (a->q_dtype == B200_BF16) return launch_generic<__nv_bfloat16>(p, a->kv_dtype, a->num_ctas, stream);
   return launch_generic<__half>(p, a->kv_dtype, a->num_ctas, stream);

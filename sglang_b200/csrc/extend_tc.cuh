@@ -114,8 +114,12 @@ __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const Extend
   const int64_t pool_row = load_index(p.req_pool_indices, p.req_pool_indices_is_i64, req);
   const int q_tok0 = qo_indptr[req] + q_start;            // first global q row of this item
   const int n_q = min(kQTiles * BQ, E - q_start);          // valid query tokens in this item
-  const int kv_end = p.causal ? P + q_start + n_q : P + E; // kv positions [0, kv_end) are needed
-  const int n_blocks = (kv_end + kBlockKV - 1) / kBlockKV;
+  const int kv_end = p.causal ? P + q_start + n_q : P + E; // kv positions [kv_off, kv_end) are needed
+  // sliding window: the first query of the item sees nothing before P + q_start + 1 - window_keys, so whole
+  // 128-token blocks below that are skipped; all three roles count blocks from kv_off
+  const int kv_first = (p.window_keys > 0 && P + q_start + 1 > p.window_keys) ? P + q_start + 1 - p.window_keys : 0;
+  const int kv_off = kv_first / kBlockKV * kBlockKV;
+  const int n_blocks = (kv_end - kv_off + kBlockKV - 1) / kBlockKV;
 
   // ---- one-time setup --------------------------------------------------------------------------
   if (threadIdx.x == 0) {

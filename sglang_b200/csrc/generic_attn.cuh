@@ -22,16 +22,19 @@ __device__ __forceinline__ float capped_logit_log2(float raw_dot, float qk_scale
 
 // One warp.  q_s: Dk floats in shared memory (already converted).  pt: page-table
 // entries of the n_tok tokens to attend.  QK: one token per lane; PV: lanes split Dv
-// and the probabilities are broadcast by shuffle.
+// and the probabilities are broadcast by shuffle.  A block of 32 tokens that is entirely masked leaves the state
+// untouched (m stays -inf until the first visible token).
 template <typename KVT>
 __device__ __forceinline__ void attend_row_generic(RowState& st, const float* q_s, const int32_t* pt, int n_tok,
                                                    const KVT* kc, const KVT* vc, int64_t k_stride_s,
                                                    int64_t v_stride_s, int64_t k_head_off, int64_t v_head_off,
-                                                   int Dk, int Dv, float qk_scale, float logit_cap) {
+                                                   int Dk, int Dv, float qk_scale, float logit_cap,
+                                                   const uint8_t* mask = nullptr, int mask_from = 0) {
   const int lane = threadIdx.x & 31;
   for (int t0 = 0; t0 < n_tok; t0 += kWarp) {
     const int tok = t0 + lane;
-    const bool valid = tok < n_tok;
+    // custom (tree) mask: token `tok` of the range is visible iff mask[tok] != 0; tokens before mask_from always are
+    const bool valid = tok < n_tok && (mask == nullptr || tok < mask_from || mask[tok] != 0);
     const int64_t slot = valid ? (int64_t)pt[tok] : 0;
     float s = -INFINITY;
     if (valid) {
@@ -41,6 +44,7 @@ __device__ __forceinline__ void attend_row_generic(RowState& st, const float* q_
       s = capped_logit_log2(dot, qk_scale, logit_cap);
     }
     const float m_new = fmaxf(st.m, warp_max(s));
+    if (m_new == -INFINITY) continue;                  // nothing visible so far
     const float pr = valid ? exp2f(s - m_new) : 0.f;
     const float corr = exp2f(st.m - m_new);
     st.l = st.l * corr + warp_sum(pr);

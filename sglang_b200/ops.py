@@ -55,6 +55,24 @@ def _index_kind(t: torch.Tensor, name: str) -> int:
     raise ValueError(f"{name} must be int32 or int64, got {t.dtype}")
 
 
+def _f32_vec(t: Optional[torch.Tensor], n: int, name: str):
+    if t is None:
+        return None
+    _need_cuda(t)
+    if t.dtype != torch.float32 or t.shape != (n,) or not t.is_contiguous():
+        raise ValueError(f"{name} must be a contiguous float32 tensor of shape ({n},)")
+    return t.data_ptr()
+
+
+def _f32_out(t: Optional[torch.Tensor], shape, name: str):
+    if t is None:
+        return None
+    _need_cuda(t)
+    if t.dtype != torch.float32 or tuple(t.shape) != tuple(shape) or not t.is_contiguous():
+        raise ValueError(f"{name} must be a contiguous float32 tensor of shape {tuple(shape)}")
+    return t.data_ptr()
+
+
 _device_info_cache = {}
 
 
@@ -223,12 +241,13 @@ class DecodeWorkspace:
 
 def decode_plan(ws: DecodeWorkspace, seq_lens: torch.Tensor, num_kv_heads: int, *, waves: int = 16,
                 min_chunk_tokens: int = 512, fixed_chunk_tokens: int = 0,
-                items_per_chunk: Optional[int] = None) -> None:
+                items_per_chunk: Optional[int] = None, window_keys: int = 0) -> None:
     """Per-forward split-KV work list, built on the device (no host sync).
 
     `items_per_chunk` (see `decode_items_per_chunk`) replaces `num_kv_heads` as the grid hint when the
     head-group kernel will run: an item then covers 4 kv heads, so the smallest useful chunk shrinks by
-    the same factor."""
+    the same factor.  `window_keys` > 0 plans only the last `window_keys` tokens of every request (sliding
+    window; pass the same value to `decode_attention`)."""
     global launch_count
     _need_cuda(seq_lens, ws.plan)
     if items_per_chunk is not None and 0 < items_per_chunk < num_kv_heads:
@@ -239,6 +258,7 @@ def decode_plan(ws: DecodeWorkspace, seq_lens: torch.Tensor, num_kv_heads: int, 
         batch_size=seq_lens.shape[0], max_bs=ws.max_bs, max_chunks=ws.max_chunks,
         num_kv_heads=num_kv_heads, num_ctas=ws.num_ctas, waves=waves,
         min_chunk_tokens=min_chunk_tokens, fixed_chunk_tokens=fixed_chunk_tokens, plan=ws.plan.data_ptr(),
+        window_keys=max(0, int(window_keys)),
     )
     _C.check(_C.lib.b200attn_decode_plan(C.byref(a), _stream()), "decode_plan")
     launch_count += 1
@@ -261,8 +281,13 @@ def decode_attention(
     logit_cap: float = 0.0,
     kernel: int = KERNEL_AUTO,
     attn_events=None,
+    window_keys: int = 0,
+    sinks: Optional[torch.Tensor] = None,
+    lse: Optional[torch.Tensor] = None,
 ) -> torch.Tensor:
-    """`attn_events`: optional (start, stop) torch.cuda.Event pair (already recorded once, so the
+    """`window_keys` > 0: sliding window over the last `window_keys` tokens (the plan must have been built with
+    the same value); `sinks`: float32 [Hq] attention-sink logits; `lse`: float32 [bs, Hq] natural-log LSE output.
+    `attn_events`: optional (start, stop) torch.cuda.Event pair (already recorded once, so the
     handles exist) that the library re-records around the attention kernel alone -- bench.py's
     live per-kernel timing."""
     global launch_count
@@ -292,6 +317,8 @@ def decode_attention(
         ws_o=ws.ws_o.data_ptr(), ws_lse=ws.ws_lse.data_ptr(), num_ctas=ws.num_ctas, kernel=kernel,
         ev_attn_start=attn_events[0].cuda_event if attn_events else None,
         ev_attn_stop=attn_events[1].cuda_event if attn_events else None,
+        window_keys=max(0, int(window_keys)), sinks=_f32_vec(sinks, Hq, "sinks"),
+        lse=_f32_out(lse, (bs, Hq), "lse"),
     )
     if ws.ws_o.numel() < ws.max_chunks * Hq * Dv or ws.ws_lse.numel() < ws.max_chunks * Hq:
         raise ValueError("decode workspace too small for this head configuration")
@@ -374,7 +401,16 @@ def extend_attention(
     causal: bool = True,
     kernel: int = KERNEL_AUTO,
     lse: Optional[torch.Tensor] = None,
+    window_keys: int = 0,
+    sinks: Optional[torch.Tensor] = None,
+    custom_mask: Optional[torch.Tensor] = None,
+    mask_indptr: Optional[torch.Tensor] = None,
+    mask_skip_prefix: bool = True,
 ) -> torch.Tensor:
+    """`window_keys` > 0: query at position x attends kv positions (x - window_keys, x].  `sinks`: float32 [Hq].
+    `custom_mask` (uint8 / bool, flat) + `mask_indptr` (int64 [bs + 1]): request r, query i, kv position x is
+    visible iff custom_mask[mask_indptr[r] + i * (P_r + E_r) + x]; it replaces the causal rule on the new tokens
+    and, unless `mask_skip_prefix`, also masks the prefix (reference extend_attention.py:378-390,525-539)."""
     global launch_count
     _need_cuda(q, o, k_cache, v_cache, req_to_token, req_pool_indices, extend_prefix_lens, extend_seq_lens)
     if q.dim() != 3 or o.dim() != 3 or k_cache.dim() != 3 or v_cache.dim() != 3:
@@ -403,9 +439,56 @@ def extend_attention(
         q_dtype=dtype_code(q.dtype), kv_dtype=dtype_code(kv_dtype or k_cache.dtype),
         sm_scale=float(sm_scale), k_scale=float(k_scale), v_scale=float(v_scale), logit_cap=float(logit_cap),
         causal=1 if causal else 0, plan=ws.plan.data_ptr(), max_bs=ws.max_bs, max_tiles=ws.max_tiles,
-        num_ctas=ws.num_ctas, kernel=kernel, lse=0 if lse is None else lse.data_ptr(),
+        num_ctas=ws.num_ctas, kernel=kernel, lse=_f32_out(lse, (T, Hq), "lse"),
         pool_slots=k_cache.shape[0],
+        window_keys=max(0, int(window_keys)), sinks=_f32_vec(sinks, Hq, "sinks"),
+        mask_skip_prefix=1 if mask_skip_prefix else 0,
     )
+    if custom_mask is not None:
+        if mask_indptr is None:
+            raise ValueError("custom_mask needs mask_indptr")
+        _need_cuda(custom_mask, mask_indptr)
+        if custom_mask.dtype not in (torch.uint8, torch.bool) or not custom_mask.is_contiguous():
+            raise ValueError("custom_mask must be a contiguous uint8 / bool tensor")
+        if mask_indptr.dtype != torch.int64 or mask_indptr.shape != (extend_seq_lens.shape[0] + 1,):
+            raise ValueError("mask_indptr must be int64 [bs + 1]")
+        a.custom_mask, a.mask_indptr = custom_mask.data_ptr(), mask_indptr.data_ptr()
     _C.check(_C.lib.b200attn_extend(C.byref(a), _stream()), "extend")
     launch_count += 1
     return o
+
+
+# --------------------------------------------------------------------------- merge of partial states
+def merge_state(o_a: torch.Tensor, lse_a: torch.Tensor, o_b: torch.Tensor, lse_b: torch.Tensor,
+                out: Optional[torch.Tensor] = None, out_lse: Optional[torch.Tensor] = None):
+    """Merge two partial attention states [T, H, D] + natural-log LSE [T, H] (chunked prefix / cascade).
+
+    Mirrors `merge_state_v2` / `merge_state_triton` (reference kernels/ops/attention/merge_state.py:69-100):
+    returns (out, out_lse); an LSE of +inf counts as an empty state."""
+    global launch_count
+    _need_cuda(o_a, lse_a, o_b, lse_b, out, out_lse)
+    if o_a.dim() != 3 or o_a.shape != o_b.shape or o_a.dtype != o_b.dtype:
+        raise ValueError("merge_state expects two [T, H, D] tensors of the same shape and dtype")
+    T, H, D = o_a.shape
+    if out is None:
+        out = torch.empty_like(o_a)
+    if out_lse is None:
+        out_lse = torch.empty((T, H), dtype=torch.float32, device=o_a.device)
+    for t, name in ((lse_a, "lse_a"), (lse_b, "lse_b"), (out_lse, "out_lse")):
+        if t.dtype != torch.float32 or tuple(t.shape) != (T, H) or not t.is_contiguous():
+            raise ValueError(f"{name} must be a contiguous float32 [T, H] tensor")
+    for t in (o_a, o_b, out):
+        if t.stride(2) != 1:
+            raise ValueError("innermost (head_dim) stride must be 1")
+    if T == 0:
+        return out, out_lse
+    a = _C.MergeStateArgs(
+        o_a=o_a.data_ptr(), lse_a=lse_a.data_ptr(), o_b=o_b.data_ptr(), lse_b=lse_b.data_ptr(),
+        o=out.data_ptr(), lse=out_lse.data_ptr(), num_tokens=T, num_heads=H, head_dim=D,
+        dtype=dtype_code(o_a.dtype),
+        oa_stride_t=o_a.stride(0), oa_stride_h=o_a.stride(1), ob_stride_t=o_b.stride(0), ob_stride_h=o_b.stride(1),
+        o_stride_t=out.stride(0), o_stride_h=out.stride(1),
+    )
+    _C.check(_C.lib.b200attn_merge_state(C.byref(a), _stream()), "merge_state")
+    launch_count += 1
+    return out, out_lse

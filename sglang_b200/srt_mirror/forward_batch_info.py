@@ -70,5 +70,6 @@ class ForwardBatch:
     # not used by dense MHA configs; kept so backends can test them for None
     encoder_lens: Optional[torch.Tensor] = None
     encoder_out_cache_loc: Optional[torch.Tensor] = None
-    spec_info: Optional[object] = None
+    spec_info: Optional[object] = None       # TARGET_VERIFY: .draft_token_num, .custom_mask
+    mha_return_lse: bool = False             # extend returns (o, lse) (radix_attention.py:244-277)
     _attn_output: Optional[torch.Tensor] = None

@@ -118,3 +118,39 @@ def run_backend_on_case(c, device="cuda", decode_kernel=0, extend_kernel=0):
                 c.v_new.to(device).reshape(T, -1), fb, backend)
     torch.cuda.synchronize()
     return out, pool
+
+
+class GoldenFeatures:
+    """tests/golden/features.npz: outputs of the reference's Triton kernels (CPU interpreter) and of
+    TorchNativeAttnBackend with sliding windows (oracle/gen_golden_features.py).  float32 throughout."""
+
+    def __init__(self):
+        self.z = np.load(GOLDEN / "features.npz")
+        self.names = [str(n) for n in self.z["names"]]
+
+    def attn_names(self):
+        return [n for n in self.names if int(self.z[f"{n}.kind"]) in (0, 1)]
+
+    def case(self, name: str) -> SimpleNamespace:
+        z = self.z
+        c = SimpleNamespace(name=name, kind=int(z[f"{name}.kind"]))
+        t = lambda k: torch.from_numpy(z[f"{name}.{k}"].copy())  # noqa: E731
+        if c.kind == 2:
+            c.o_a, c.lse_a, c.o_b, c.lse_b, c.out, c.lse = (t(k) for k in ("o_a", "lse_a", "o_b", "lse_b", "out", "lse"))
+            return c
+        c.is_decode = c.kind == 1
+        c.q, c.k_pool, c.v_pool = t("q"), t("k_pool"), t("v_pool")
+        c.req_to_token, c.req_pool_indices = t("req_to_token"), t("req_pool_indices")
+        c.prefix_lens, c.extend_lens = t("prefix_lens"), t("extend_lens")
+        opts = z[f"{name}.opts"]
+        c.logit_cap, c.window_keys = float(opts[0]), int(opts[1])
+        c.mask_skip_prefix, c.causal = bool(opts[2]), bool(opts[3])
+        c.sinks = t("sinks") if z[f"{name}.sinks"].size else None
+        c.custom_mask = t("custom_mask") if z[f"{name}.custom_mask"].size else None
+        c.mask_indptr = t("mask_indptr") if z[f"{name}.mask_indptr"].size else None
+        c.out = t("out")
+        c.lse = t("lse") if z[f"{name}.lse"].size else None
+        c.Hq, c.D = c.q.shape[1], c.q.shape[2]
+        c.Hkv = c.k_pool.shape[1]
+        c.scale = c.D ** -0.5
+        return c

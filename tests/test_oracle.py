@@ -130,3 +130,35 @@ def test_rope_cache_formula():
     c = rope_ref.cos_sin_cache(64, 32, 10000.0)
     assert c.shape == (32, 64) and torch.all(c[0, :32] == 1) and torch.all(c[0, 32:] == 0)
     assert abs(float(c[1, 0]) - np.cos(1.0)) < 1e-6 and abs(float(c[3, 32]) - np.sin(3.0)) < 1e-6
+
+
+# ----------------------------------------------------------------------------- feature options
+from helpers import GoldenFeatures  # noqa: E402
+
+_FEAT = GoldenFeatures()
+
+
+@pytest.mark.parametrize("name", _FEAT.attn_names())
+def test_oracle_features_match_reference_kernels(name):
+    """Sinks / logit cap / sliding window / custom masks / LSE: the oracle equals the reference's own Triton
+    kernels (run by Triton's CPU interpreter) and TorchNativeAttnBackend with sliding windows, in float32."""
+    c = _FEAT.case(name)
+    if c.is_decode:
+        got = ref.decode_ref(c.q, c.k_pool, c.v_pool, c.req_to_token, c.req_pool_indices, c.prefix_lens, c.scale,
+                             logit_cap=c.logit_cap, window_keys=c.window_keys, sinks=c.sinks)
+        lse = None
+    else:
+        got, lse = ref.extend_ref(c.q, c.k_pool, c.v_pool, c.req_to_token, c.req_pool_indices, c.prefix_lens,
+                                  c.extend_lens, c.scale, logit_cap=c.logit_cap, causal=c.causal,
+                                  window_keys=c.window_keys, sinks=c.sinks, custom_mask=c.custom_mask,
+                                  mask_indptr=c.mask_indptr, mask_skip_prefix=c.mask_skip_prefix, want_lse=True)
+    assert (got - c.out.view_as(got)).abs().max().item() < 2e-5, name
+    if c.lse is not None:
+        assert (lse - c.lse).abs().max().item() < 2e-5, name
+
+
+def test_merge_state_ref_matches_reference_kernel():
+    c = _FEAT.case("merge_basic")
+    out, lse = ref.merge_state_ref(c.o_a, c.lse_a, c.o_b, c.lse_b)
+    assert torch.allclose(out, c.out, atol=1e-6, equal_nan=True)
+    assert torch.allclose(lse, c.lse, atol=1e-6, equal_nan=True)
