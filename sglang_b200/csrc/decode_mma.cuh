@@ -159,6 +159,7 @@ __global__ void __launch_bounds__(kFastWarps* kWarp, (FastCfg<D, KV>::kCtaSmem >
   const float scale_log2 = p.sm_scale * p.k_scale * kLog2e;
   const bool capped = p.logit_cap > 0.f;               // s = cap * tanh(s * sm_scale / cap)
   const float cap_in = capped ? p.sm_scale * p.k_scale / p.logit_cap : 0.f, cap_out = p.logit_cap * kLog2e;
+  const float score_mul = capped ? 1.f : scale_log2;
   const uint8_t* kc = reinterpret_cast<const uint8_t*>(p.k_cache);
   const uint8_t* vc = reinterpret_cast<const uint8_t*>(p.v_cache);
   const int64_t k_slot_b = p.k_stride_s * C::kEsz, v_slot_b = p.v_stride_s * C::kEsz;
@@ -292,12 +293,18 @@ __global__ void __launch_bounds__(kFastWarps* kWarp, (FastCfg<D, KV>::kCtaSmem >
       // ---- online softmax (base 2) ----
       const int tok0 = T * kTileTok + 2 * quad;  // token (within this warp's slice) of s_acc[0][0]
       float pmax[2] = {-INFINITY, -INFINITY};
+      if (capped) {                                        // warp-uniform; the common path below is unchanged
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) s_acc[nt][e] = cap_out * tanh_ex2(s_acc[nt][e] * cap_in);
+      }
 #pragma unroll
       for (int nt = 0; nt < 2; ++nt) {
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const int tok = tok0 + 8 * nt + (e & 1);
-          float v = capped ? cap_out * tanh_ex2(s_acc[nt][e] * cap_in) : s_acc[nt][e] * scale_log2;
+          float v = s_acc[nt][e] * score_mul;
           if (tok >= w_ntok) v = -INFINITY;
           s_acc[nt][e] = v;
           if (UPPER || e < 2) pmax[e >> 1] = fmaxf(pmax[e >> 1], v);

@@ -83,7 +83,8 @@ __device__ __forceinline__ uint32_t swz_off(int row, int chunk, int rows) {
 // kEmu: how many of every 8 column pairs take the polynomial exp2 (FMA pipe) instead of MUFU.EX2.
 // kFp8: the pool holds FP8-e4m3 bytes; the MMAs then run in f16 (e4m3 -> f16 is exact) on tiles the producers
 // dequantise, Q is converted to f16 on its way into shared memory and P is packed as f16.
-template <typename QT, int kEmu, bool kFp8>
+// kOpts: sliding window / logit cap / attention sinks compiled in (the plain causal instance stays untouched).
+template <typename QT, int kEmu, bool kFp8, bool kOpts>
 __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const ExtendParams p, const int max_tiles) {
   using namespace tc;
   using namespace ptx;
@@ -117,7 +118,8 @@ __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const Extend
   const int kv_end = p.causal ? P + q_start + n_q : P + E; // kv positions [kv_off, kv_end) are needed
   // sliding window: the first query of the item sees nothing before P + q_start + 1 - window_keys, so whole
   // 128-token blocks below that are skipped; all three roles count blocks from kv_off
-  const int kv_first = (p.window_keys > 0 && P + q_start + 1 > p.window_keys) ? P + q_start + 1 - p.window_keys : 0;
+  const int kv_first =
+      (kOpts && p.window_keys > 0 && P + q_start + 1 > p.window_keys) ? P + q_start + 1 - p.window_keys : 0;
   const int kv_off = kv_first / kBlockKV * kBlockKV;
   const int n_blocks = (kv_end - kv_off + kBlockKV - 1) / kBlockKV;
 
@@ -187,11 +189,11 @@ bool extend_fast_layout_ok(const ExtendParams& p, int kv_dtype) {
          p.k_stride_s > 0 && p.v_stride_s > 0 && p.k_stride_s < (1ll << 30) && p.v_stride_s < (1ll << 30);
 }
 
-template <typename QT, int kEmu, bool kFp8>
+template <typename QT, int kEmu, bool kFp8, bool kOpts>
 int launch_extend_fast_t(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   static bool configured = false;
   constexpr int kSmem = tc::Layout<kFp8>::kSmemBytes;
-  auto kern = extend_tc_kernel<QT, kEmu, kFp8>;
+  auto kern = extend_tc_kernel<QT, kEmu, kFp8, kOpts>;
   if (!configured) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     configured = true;
@@ -207,26 +209,25 @@ int launch_extend_fast_t(const ExtendParams& p, const b200_extend_args& a, cudaS
   return B200_OK;
 }
 
-// Share of exp2 evaluated by the polynomial (eighths).  B200ATTN_EXTEND_EMU overrides the tuned default;
-// it is a tuning aid, both paths are within 1e-4 relative of each other.
+// Share of exp2 evaluated by the polynomial (eighths): 3 is the tuned default, B200ATTN_EXTEND_EMU=0 turns the
+// polynomial off (A/B aid; both paths are within 1e-4 relative of each other).
 int extend_emu_eighths() {
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("B200ATTN_EXTEND_EMU");
-    v = e ? atoi(e) : 3;
-    if (v < 0 || v > 3) v = 3;
+    v = (e && atoi(e) == 0) ? 0 : 3;
   }
   return v;
 }
 
 template <typename QT, bool kFp8>
 int launch_extend_fast_q(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
-  switch (extend_emu_eighths()) {
-    case 0: return launch_extend_fast_t<QT, 0, kFp8>(p, a, stream);
-    case 1: return launch_extend_fast_t<QT, 1, kFp8>(p, a, stream);
-    case 2: return launch_extend_fast_t<QT, 2, kFp8>(p, a, stream);
-    default: return launch_extend_fast_t<QT, 3, kFp8>(p, a, stream);
-  }
+  const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr;
+  if (extend_emu_eighths() == 0)
+    return opts ? launch_extend_fast_t<QT, 0, kFp8, true>(p, a, stream)
+                : launch_extend_fast_t<QT, 0, kFp8, false>(p, a, stream);
+  return opts ? launch_extend_fast_t<QT, 3, kFp8, true>(p, a, stream)
+              : launch_extend_fast_t<QT, 3, kFp8, false>(p, a, stream);
 }
 
 int launch_extend_fast(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {

@@ -283,12 +283,12 @@ extern "C" int b200attn_rope_store_kv(const b200_rope_store_args* a, b200_stream
   p.k_scale = a->k_scale; p.v_scale = a->v_scale;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   const int s = a->src_dtype, d = a->k_cache ? a->dst_dtype : a->src_dtype;
-  if (s == B200_BF16 && d == B200_BF16) return launch_rope_store<__nv_bfloat16, __nv_bfloat16>(p, stream);
-  if (s == B200_F16 && d == B200_F16) return launch_rope_store<__half, __half>(p, stream);
-  if (s == B200_BF16 && d == B200_FP8_E4M3) return launch_rope_store<__nv_bfloat16, e4m3_t>(p, stream);
-  if (s == B200_F16 && d == B200_FP8_E4M3) return launch_rope_store<__half, e4m3_t>(p, stream);
-  if (s == B200_BF16 && d == B200_FP8_E5M2) return launch_rope_store<__nv_bfloat16, e5m2_t>(p, stream);
-  if (s == B200_F16 && d == B200_FP8_E5M2) return launch_rope_store<__half, e5m2_t>(p, stream);
+  if (s == B200_BF16 && d == B200_BF16) return launch_rope_any<__nv_bfloat16, __nv_bfloat16>(p, stream);
+  if (s == B200_F16 && d == B200_F16) return launch_rope_any<__half, __half>(p, stream);
+  if (s == B200_BF16 && d == B200_FP8_E4M3) return launch_rope_any<__nv_bfloat16, e4m3_t>(p, stream);
+  if (s == B200_F16 && d == B200_FP8_E4M3) return launch_rope_any<__half, e4m3_t>(p, stream);
+  if (s == B200_BF16 && d == B200_FP8_E5M2) return launch_rope_any<__nv_bfloat16, e5m2_t>(p, stream);
+  if (s == B200_F16 && d == B200_FP8_E5M2) return launch_rope_any<__half, e5m2_t>(p, stream);
   set_error("rope_store_kv: unsupported dtype pair src=%d dst=%d", s, d);
   return B200_EINVAL;
 }

@@ -233,3 +233,219 @@ int launch_rope_store(const RopeParams& p, cudaStream_t stream) {
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;
 }
+
+// ------------------------------------------------------------------------------------------------------------
+// Fast path: full rotary (rotary_dim == head_dim == v_head_dim, D in {64, 128, 256}).
+//
+// The first kernel above spends its time on per-thread index arithmetic (a 64-bit division and several 32-bit
+// ones per 32 bytes) and re-reads the cos/sin row once per head.  Here a WARP owns a slice of one token:
+//   * lane -> (head within the pass, 16-byte chunk j of the first half of the head): TPH = D/16 lanes per head,
+//     HPP = 32/TPH heads per warp pass; the lane also owns chunk j + TPH (the neox partner, or simply the second
+//     half of the head for the interleaved layout) -- both loads of a pass hit whole 128-byte lines;
+//   * the cos/sin values of the lane's chunk are loaded ONCE per token and reused for every q and k head;
+//   * passes of a token: ceil(Hq/HPP) q passes, ceil(Hkv/HPP) k passes, then v passes (plain 2 x 512-byte copies);
+//     kBatch passes are loaded before the first dependent use (the in-place q/k stores would otherwise order
+//     every load behind the previous store);
+//   * `slices` warps share a token when there are few tokens (decode), one warp takes the whole token at prefill.
+// ------------------------------------------------------------------------------------------------------------
+struct RopeFastParams {
+  RopeParams b;
+  int32_t nq_pass, nk_pass, nv_pass;   // passes per token
+  int32_t slices, pass_per_slice;
+};
+
+constexpr int kRopeBatch = 4;
+constexpr int kRopeWarps = 4;
+
+template <typename SRC, typename DST, int D, bool NEOX>
+__global__ void __launch_bounds__(kRopeWarps * 32) rope_store_fast_kernel(const RopeFastParams fp) {
+  constexpr int TPH = D / 16, HPP = 32 / TPH;
+  const RopeParams& p = fp.b;
+  const int lane = threadIdx.x & 31;
+  const int64_t item = (int64_t)blockIdx.x * kRopeWarps + (threadIdx.x >> 5);
+  const int64_t token = item / fp.slices;
+  if (token >= p.num_tokens) return;
+  const int slice = (int)(item - token * fp.slices);
+  const int n_pass = fp.nq_pass + fp.nk_pass + fp.nv_pass;
+  const int p_begin = slice * fp.pass_per_slice;
+  const int p_end = min(n_pass, p_begin + fp.pass_per_slice);
+  if (p_begin >= p_end) return;
+  const int j = lane % TPH, hsub = lane / TPH;
+
+  // ---- pool slot (k / v passes only) ----
+  int64_t slot = -1;
+  bool store = false;
+  if (p.k_cache != nullptr && p_end > fp.nq_pass) {
+    slot = load_index(p.loc, p.loc_is_i64, token);
+    store = slot != p.skip_index;
+    if (store && (slot < 0 || slot >= p.size_limit)) {
+      if (lane == 0) printf("b200attn rope_store_kv: slot %lld out of [0, %lld)\n", (long long)slot, (long long)p.size_limit);
+      __trap();
+    }
+  }
+
+  // ---- cos / sin of this lane's chunks, once per token ----
+  float c[8], s[8];    // neox: pair index 8j + e.   interleaved: [0,4) pairs of chunk j, [4,8) pairs of chunk j + TPH
+  if (p_begin < fp.nq_pass + fp.nk_pass) {
+    const int64_t pos = load_index(p.positions, p.positions_is_i64, token);
+    if (pos < 0 || pos >= p.max_position) {
+      if (lane == 0) printf("b200attn rope_store_kv: position %lld out of [0, %lld)\n", (long long)pos, (long long)p.max_position);
+      __trap();
+    }
+    constexpr int half = D / 2;
+    if (p.cache_is_f32) {
+      const float* row = reinterpret_cast<const float*>(p.cache) + pos * D;
+      if constexpr (NEOX) {
+        const float4 c0 = __ldg(reinterpret_cast<const float4*>(row + 8 * j)), c1 = __ldg(reinterpret_cast<const float4*>(row + 8 * j + 4));
+        const float4 s0 = __ldg(reinterpret_cast<const float4*>(row + half + 8 * j)), s1 = __ldg(reinterpret_cast<const float4*>(row + half + 8 * j + 4));
+        c[0] = c0.x; c[1] = c0.y; c[2] = c0.z; c[3] = c0.w; c[4] = c1.x; c[5] = c1.y; c[6] = c1.z; c[7] = c1.w;
+        s[0] = s0.x; s[1] = s0.y; s[2] = s0.z; s[3] = s0.w; s[4] = s1.x; s[5] = s1.y; s[6] = s1.z; s[7] = s1.w;
+      } else {
+        const float4 c0 = __ldg(reinterpret_cast<const float4*>(row + 4 * j)), c1 = __ldg(reinterpret_cast<const float4*>(row + 4 * (j + TPH)));
+        const float4 s0 = __ldg(reinterpret_cast<const float4*>(row + half + 4 * j)), s1 = __ldg(reinterpret_cast<const float4*>(row + half + 4 * (j + TPH)));
+        c[0] = c0.x; c[1] = c0.y; c[2] = c0.z; c[3] = c0.w; c[4] = c1.x; c[5] = c1.y; c[6] = c1.z; c[7] = c1.w;
+        s[0] = s0.x; s[1] = s0.y; s[2] = s0.z; s[3] = s0.w; s[4] = s1.x; s[5] = s1.y; s[6] = s1.z; s[7] = s1.w;
+      }
+    } else {
+      const SRC* row = reinterpret_cast<const SRC*>(p.cache) + pos * D;
+      if constexpr (NEOX) {
+        unpack8<SRC>(__ldg(reinterpret_cast<const uint4*>(row + 8 * j)), c);
+        unpack8<SRC>(__ldg(reinterpret_cast<const uint4*>(row + half + 8 * j)), s);
+      } else {
+        const uint2 c0 = __ldg(reinterpret_cast<const uint2*>(row + 4 * j)), c1 = __ldg(reinterpret_cast<const uint2*>(row + 4 * (j + TPH)));
+        const uint2 s0 = __ldg(reinterpret_cast<const uint2*>(row + half + 4 * j)), s1 = __ldg(reinterpret_cast<const uint2*>(row + half + 4 * (j + TPH)));
+        unpack8<SRC>(make_uint4(c0.x, c0.y, c1.x, c1.y), c);
+        unpack8<SRC>(make_uint4(s0.x, s0.y, s1.x, s1.y), s);
+      }
+    }
+    if (p.native) {   // forward_native casts the cache to the activation dtype before multiplying
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { c[e] = round_to_src<SRC>(c[e]); s[e] = round_to_src<SRC>(s[e]); }
+    }
+  }
+
+  SRC* qrow = reinterpret_cast<SRC*>(p.q) + token * p.q_stride_t;
+  SRC* krow = reinterpret_cast<SRC*>(p.k) + token * p.k_stride_t;
+  const SRC* vrow = reinterpret_cast<const SRC*>(p.v) + token * p.v_stride_t;
+  DST* kdst = store ? reinterpret_cast<DST*>(p.k_cache) + slot * p.k_cache_stride : nullptr;
+  DST* vdst = store ? reinterpret_cast<DST*>(p.v_cache) + slot * p.v_cache_stride : nullptr;
+  const bool k_scaled = p.k_scale != 1.0f, v_scaled = p.v_scale != 1.0f;
+  const int v_chunks = p.Hkv * (D / 8);                       // 16-byte chunks of the token's V row
+
+  for (int p0 = p_begin; p0 < p_end; p0 += kRopeBatch) {
+    uint4 a[kRopeBatch], b[kRopeBatch];
+    int off[kRopeBatch];          // element offset of the lane's first chunk inside the token row; -1 = idle
+    // ---- issue every load of the batch ----
+#pragma unroll
+    for (int u = 0; u < kRopeBatch; ++u) {
+      const int ps = p0 + u;
+      off[u] = -1;
+      a[u] = b[u] = make_uint4(0u, 0u, 0u, 0u);
+      if (ps >= p_end) continue;
+      if (ps < fp.nq_pass + fp.nk_pass) {
+        const bool is_q = ps < fp.nq_pass;
+        const int head = (is_q ? ps : ps - fp.nq_pass) * HPP + hsub;
+        if (head < (is_q ? p.Hq : p.Hkv)) {
+          off[u] = head * D + 8 * j;
+          const SRC* src = (is_q ? qrow : krow) + off[u];
+          a[u] = ld_16(src);
+          b[u] = ld_16(src + D / 2);
+        }
+      } else if (store) {
+        const int ch = (ps - fp.nq_pass - fp.nk_pass) * 64 + lane;      // chunks ch and ch + 32
+        if (ch < v_chunks) {
+          off[u] = ch * 8;
+          a[u] = ld_stream_16(vrow + off[u]);
+          if (ch + 32 < v_chunks) b[u] = ld_stream_16(vrow + off[u] + 256);
+        }
+      }
+    }
+    // ---- rotate / convert / store ----
+#pragma unroll
+    for (int u = 0; u < kRopeBatch; ++u) {
+      const int ps = p0 + u;
+      if (off[u] < 0) continue;
+      if (ps >= fp.nq_pass + fp.nk_pass) {                    // V: pool store only
+        finish_vec8<SRC, DST>(a[u], vdst + off[u], p.v_scale, v_scaled);
+        if (off[u] / 8 + 32 < v_chunks) finish_vec8<SRC, DST>(b[u], vdst + off[u] + 256, p.v_scale, v_scaled);
+        continue;
+      }
+      const bool is_q = ps < fp.nq_pass;
+      float x1[8], x2[8], o1[8], o2[8];
+      unpack8<SRC>(a[u], x1);
+      unpack8<SRC>(b[u], x2);
+      if constexpr (NEOX) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) rotate_pair<SRC>(p.native != 0, x1[e], x2[e], c[e], s[e], o1[e], o2[e]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          rotate_pair<SRC>(p.native != 0, x1[2 * e], x1[2 * e + 1], c[e], s[e], o1[2 * e], o1[2 * e + 1]);
+          rotate_pair<SRC>(p.native != 0, x2[2 * e], x2[2 * e + 1], c[4 + e], s[4 + e], o2[2 * e], o2[2 * e + 1]);
+        }
+      }
+      const uint4 r1 = pack8<SRC>(o1), r2 = pack8<SRC>(o2);
+      if (is_q || p.write_k) {
+        SRC* dst = (is_q ? qrow : krow) + off[u];
+        *reinterpret_cast<uint4*>(dst) = r1;
+        *reinterpret_cast<uint4*>(dst + D / 2) = r2;
+      }
+      if (!is_q && store) {
+        finish_vec8<SRC, DST>(r1, kdst + off[u], p.k_scale, k_scaled);
+        finish_vec8<SRC, DST>(r2, kdst + off[u] + D / 2, p.k_scale, k_scaled);
+      }
+    }
+  }
+}
+
+inline bool rope_fast_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200ATTN_ROPE_FAST");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
+
+template <typename SRC, typename DST, int D, bool NEOX>
+int launch_rope_fast_inst(const RopeParams& p, cudaStream_t stream) {
+  constexpr int HPP = 32 / (D / 16);
+  RopeFastParams fp;
+  fp.b = p;
+  fp.nq_pass = (p.Hq + HPP - 1) / HPP;
+  fp.nk_pass = (p.Hkv + HPP - 1) / HPP;
+  fp.nv_pass = p.k_cache != nullptr ? (p.Hkv * (D / 8) + 63) / 64 : 0;
+  const int n_pass = fp.nq_pass + fp.nk_pass + fp.nv_pass;
+  // enough warps to fill the machine: one per token at prefill, several per token for small batches
+  const int64_t want_warps = (int64_t)sm_count() * 32;
+  int slices = 1;
+  if (p.num_tokens < want_warps) {
+    slices = (int)((want_warps + p.num_tokens - 1) / p.num_tokens);
+    if (slices > n_pass) slices = n_pass;
+  }
+  fp.pass_per_slice = (n_pass + slices - 1) / slices;
+  fp.slices = (n_pass + fp.pass_per_slice - 1) / fp.pass_per_slice;
+  const int64_t warps = p.num_tokens * fp.slices;
+  const int64_t blocks = (warps + kRopeWarps - 1) / kRopeWarps;
+  B200_CHECK_ARG(blocks > 0 && blocks < (int64_t)0x7fffffff, "rope_store_kv: too many rows (%lld)",
+                 (long long)p.num_tokens);
+  rope_store_fast_kernel<SRC, DST, D, NEOX><<<(unsigned)blocks, kRopeWarps * 32, 0, stream>>>(fp);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+// full rotary with D = Dv in {64, 128, 256}: the warp-per-token kernel; everything else: the per-unit kernel
+template <typename SRC, typename DST>
+int launch_rope_any(const RopeParams& p, cudaStream_t stream) {
+  const bool fast = rope_fast_enabled() && p.rot == p.D && (p.k_cache == nullptr || p.Dv == p.D) &&
+                    (p.D == 64 || p.D == 128 || p.D == 256);
+  if (!fast) return launch_rope_store<SRC, DST>(p, stream);
+  if (p.is_neox) {
+    if (p.D == 64) return launch_rope_fast_inst<SRC, DST, 64, true>(p, stream);
+    if (p.D == 128) return launch_rope_fast_inst<SRC, DST, 128, true>(p, stream);
+    return launch_rope_fast_inst<SRC, DST, 256, true>(p, stream);
+  }
+  if (p.D == 64) return launch_rope_fast_inst<SRC, DST, 64, false>(p, stream);
+  if (p.D == 128) return launch_rope_fast_inst<SRC, DST, 128, false>(p, stream);
+  return launch_rope_fast_inst<SRC, DST, 256, false>(p, stream);
+}

@@ -91,3 +91,53 @@ def test_rope_store_rejects_bad_shapes():
         ops.rope_store_kv(torch.arange(4, device="cuda"), q, k, None, cache, 128)
     with pytest.raises(ValueError):
         ops.rope_store_kv(torch.arange(4, device="cuda"), q, k, None, cache.double(), 128)
+
+
+@pytest.mark.parametrize("T,Hq,Hkv,D,neox,pool_dt", [
+    (5000, 32, 8, 128, True, None),                  # one warp per token (prefill regime), Llama-8B heads
+    (5000, 32, 8, 128, True, torch.float8_e4m3fn),
+    (600, 32, 8, 128, False, torch.float8_e4m3fn),   # a token shared by several warps, interleaved pairs
+    (64, 32, 8, 128, True, None),                    # decode regime: one pass per warp
+    (333, 14, 2, 64, True, None),                    # Qwen2.5-0.5B heads: partial passes (8 heads per pass)
+    (97, 64, 8, 64, True, torch.float8_e4m3fn),      # gpt-oss heads
+    (130, 8, 4, 256, False, None),                   # D 256: 2 heads per pass
+    (130, 16, 16, 256, True, torch.float8_e5m2),
+])
+def test_rope_store_warp_per_token_shapes(T, Hq, Hkv, D, neox, pool_dt):
+    """The full-rotary fast path at the shapes that decide its work split; native rounding -> bit-exact."""
+    from sglang_b200 import ops
+
+    g = torch.Generator().manual_seed(T + D)
+    dt = torch.bfloat16
+    pdt = pool_dt or dt
+    rows = T + 9
+    cache = rope_ref.cos_sin_cache(D, 4096, 10000.0, torch.float32)
+    pos = torch.randint(0, 4096, (T,), generator=g)
+    q = torch.randn(T, Hq * D, generator=g).to(dt)
+    k = torch.randn(T, Hkv * D, generator=g).to(dt)
+    v = torch.randn(T, Hkv * D, generator=g).to(dt)
+    loc = torch.randperm(rows - 1, generator=g)[:T] + 1
+    loc[T // 2] = 0
+    want_q, want_k = rope_ref.rope_ref(pos, q, k, cache, D, neox, native_rounding=True)
+    for write_k in (True, False):
+        qd, kd, vd = q.cuda(), k.cuda(), v.cuda()
+        kc = torch.zeros(rows, Hkv, D, dtype=store_dtype(pdt), device="cuda")
+        vc = torch.zeros_like(kc)
+        ops.rope_store_kv(pos.cuda(), qd, kd, vd, cache.cuda(), D, is_neox=neox, k_cache=kc, v_cache=vc,
+                          loc=loc.cuda(), cache_dtype=pdt, native_rounding=True, write_k=write_k)
+        torch.cuda.synchronize()
+        assert torch.equal(qd.cpu().view(torch.int16), want_q.view(torch.int16))
+        assert torch.equal(kd.cpu().view(torch.int16), (want_k if write_k else k).view(torch.int16))
+        assert torch.equal(vd.cpu().view(torch.int16), v.view(torch.int16))
+        kc_ref = torch.zeros(rows, Hkv, D, dtype=store_dtype(pdt))
+        vc_ref = torch.zeros_like(kc_ref)
+        ref.store_kv_ref(want_k.view(T, Hkv, D), v.view(T, Hkv, D), kc_ref, vc_ref, loc, cache_dtype=pdt,
+                         skip_index=0)
+        assert torch.equal(kc.cpu().view(torch.uint8), kc_ref.view(torch.uint8))
+        assert torch.equal(vc.cpu().view(torch.uint8), vc_ref.view(torch.uint8))
+    # rotate only (no pool): q and k still rotated
+    qd, kd = q.cuda(), k.cuda()
+    ops.rope_store_kv(pos.cuda(), qd, kd, None, cache.cuda(), D, is_neox=neox, native_rounding=True)
+    torch.cuda.synchronize()
+    assert torch.equal(qd.cpu().view(torch.int16), want_q.view(torch.int16))
+    assert torch.equal(kd.cpu().view(torch.int16), want_k.view(torch.int16))
