@@ -25,6 +25,7 @@
  *   b200attn_extend          srt/layers/attention/torch_native_backend.py:61-174 (oracle semantics),
  *                            kernels/ops/attention/extend_attention.py:664-812 (extend_attention_fwd)
  *   b200attn_merge_state     kernels/aot/csrc/attention/merge_attn_states.cu, kernels/ops/attention/merge_state.py
+ *   b200attn_oproj_allreduce srt/layers/linear.py:1563 (RowParallelLinear all-reduce), custom_all_reduce_v2.py
  */
 #ifndef B200ATTN_H_
 #define B200ATTN_H_
@@ -35,7 +36,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 2
+#define B200ATTN_ABI_VERSION 3
 
 typedef void* b200_stream_t; /* a cudaStream_t */
 
@@ -338,6 +339,45 @@ typedef struct b200_merge_state_args {
 } b200_merge_state_args;
 
 int b200attn_merge_state(const b200_merge_state_args* args, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------ *
+ * o_proj GEMM fused with its tensor-parallel all-reduce: on every rank r of the group
+ *   out[T, N] = sum_r  x_r[T, K_r] . w_r[N, K_r]^T        (w_r = this rank's column shard of the weight)
+ * Stands in for RowParallelLinear.forward -> tensor_model_parallel_all_reduce
+ * (srt/layers/linear.py:1563, srt/distributed/communication_op.py:18-20, parallel_state.py:622) and the
+ * custom all-reduce it would use (srt/distributed/device_communicators/custom_all_reduce_v2.py,
+ * kernels/jit/csrc/distributed/custom_all_reduce.cuh).  One launch per rank, same arguments on every rank
+ * except rank / x / w.  The caller owns three SYMMETRIC buffers (same size on every rank, each rank's copy
+ * mapped into every other rank: CUDA IPC or a VMM/multicast allocation):
+ *   staging  [max_tokens, N] dtype   this rank's partial products
+ *   out      [max_tokens, N] dtype   the reduced result (valid on every rank when the kernel completes)
+ *   flags    b200attn_oproj_allreduce_flag_words(max_tiles) uint32, zero-initialised once
+ * `epoch` must be non-zero and different from the previous call's (1, 2, 3, ...).  `*_mc` are the multicast
+ * (NVLS) addresses of staging / out, or NULL to reduce with peer loads.  world == 1 runs the GEMM alone and
+ * writes out_peers[0].  All ranks must launch; a missing peer traps after ~2 s instead of hanging.
+ * ------------------------------------------------------------------------ */
+#define B200_MAX_WORLD 8
+typedef struct b200_oproj_allreduce_args {
+  const void* x;             /* [T, K] dtype, row stride x_stride elements */
+  const void* w;             /* [N, K] dtype (torch Linear layout), row stride w_stride elements */
+  int64_t x_stride, w_stride;
+  int32_t num_tokens;        /* T */
+  int32_t out_features;      /* N, multiple of 64 */
+  int32_t in_features;       /* K (this rank's shard), multiple of 64 */
+  int32_t dtype;             /* B200_BF16 / B200_F16 */
+  int32_t rank, world;
+  uint32_t epoch;
+  int32_t max_tiles;         /* capacity of the flag area, >= b200attn_oproj_allreduce_tiles(T, N) */
+  void* staging_peers[B200_MAX_WORLD];
+  void* out_peers[B200_MAX_WORLD];
+  void* flags_peers[B200_MAX_WORLD];
+  void* staging_mc;
+  void* out_mc;
+} b200_oproj_allreduce_args;
+
+int b200attn_oproj_allreduce(const b200_oproj_allreduce_args* args, b200_stream_t stream);
+int64_t b200attn_oproj_allreduce_flag_words(int32_t max_tiles);
+int32_t b200attn_oproj_allreduce_tiles(int32_t num_tokens, int32_t out_features);
 
 #ifdef __cplusplus
 }

@@ -14,7 +14,7 @@ LIB_PATH = Path(os.environ.get("B200ATTN_LIB", _PKG_DIR / "lib" / "libb200attn.s
 
 B200_BF16, B200_F16, B200_FP8_E4M3, B200_FP8_E5M2 = 0, 1, 2, 3
 KERNEL_AUTO, KERNEL_GENERIC, KERNEL_FAST = 0, 1, 2
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 i32, i64, f32, vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
@@ -107,6 +107,19 @@ class MergeStateArgs(C.Structure):
     ]
 
 
+MAX_WORLD = 8
+
+
+class OProjAllReduceArgs(C.Structure):
+    _fields_ = [
+        ("x", vp), ("w", vp), ("x_stride", i64), ("w_stride", i64),
+        ("num_tokens", i32), ("out_features", i32), ("in_features", i32), ("dtype", i32),
+        ("rank", i32), ("world", i32), ("epoch", C.c_uint32), ("max_tiles", i32),
+        ("staging_peers", vp * MAX_WORLD), ("out_peers", vp * MAX_WORLD), ("flags_peers", vp * MAX_WORLD),
+        ("staging_mc", vp), ("out_mc", vp),
+    ]
+
+
 # name -> (restype, argtypes); the test-suite checks this list against include/b200attn.h
 SYMBOLS = {
     "b200attn_last_error": (C.c_char_p, []),
@@ -126,6 +139,9 @@ SYMBOLS = {
     "b200attn_extend_fast_supported": (C.c_int, [i32] * 5),
     "b200attn_extend_block_q": (C.c_int, [i32] * 6),
     "b200attn_merge_state": (C.c_int, [C.POINTER(MergeStateArgs), vp]),
+    "b200attn_oproj_allreduce": (C.c_int, [C.POINTER(OProjAllReduceArgs), vp]),
+    "b200attn_oproj_allreduce_flag_words": (i64, [i32]),
+    "b200attn_oproj_allreduce_tiles": (i32, [i32, i32]),
 }
 
 

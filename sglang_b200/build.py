@@ -20,7 +20,7 @@ CSRC = PKG_DIR / "csrc"
 LIB_DIR = PKG_DIR / "lib"
 LIB_PATH = LIB_DIR / "libb200attn.so"
 
-CU_SOURCES = ["abi.cu", "kv_store.cu", "decode.cu", "extend.cu", "merge_state.cu"]
+CU_SOURCES = ["abi.cu", "kv_store.cu", "decode.cu", "extend.cu", "merge_state.cu", "oproj_allreduce.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
