@@ -349,30 +349,36 @@ int b200attn_merge_state(const b200_merge_state_args* args, b200_stream_t stream
  * kernels/jit/csrc/distributed/custom_all_reduce.cuh).  One launch per rank, same arguments on every rank
  * except rank / x / w.  The caller owns three SYMMETRIC buffers (same size on every rank, each rank's copy
  * mapped into every other rank: CUDA IPC or a VMM/multicast allocation):
- *   staging  [max_tokens, N] dtype   this rank's partial products
+ *   staging  2 x [max_tokens, N] dtype   this rank's partial products (two buffers, alternating by launch)
  *   out      [max_tokens, N] dtype   the reduced result (valid on every rank when the kernel completes)
  *   flags    b200attn_oproj_allreduce_flag_words(max_tiles) uint32, zero-initialised once
- * `epoch` must be non-zero and different from the previous call's (1, 2, 3, ...).  `*_mc` are the multicast
+ * The call sequence number that separates one launch's flags from the next lives in the flag area and is
+ * advanced by the kernel itself, so the launch is CUDA-graph capturable and replayable.  `*_mc` are the multicast
  * (NVLS) addresses of staging / out, or NULL to reduce with peer loads.  world == 1 runs the GEMM alone and
  * writes out_peers[0].  All ranks must launch; a missing peer traps after ~2 s instead of hanging.
  * ------------------------------------------------------------------------ */
 #define B200_MAX_WORLD 8
+enum { B200_OAR_AUTO = 0, B200_OAR_ONE_SHOT = 1, B200_OAR_TWO_SHOT = 2 };
 typedef struct b200_oproj_allreduce_args {
   const void* x;             /* [T, K] dtype, row stride x_stride elements */
   const void* w;             /* [N, K] dtype (torch Linear layout), row stride w_stride elements */
   int64_t x_stride, w_stride;
   int32_t num_tokens;        /* T */
   int32_t out_features;      /* N, multiple of 64 */
-  int32_t in_features;       /* K (this rank's shard), multiple of 64 */
+  int32_t in_features;       /* K (this rank's shard), multiple of 128 */
   int32_t dtype;             /* B200_BF16 / B200_F16 */
   int32_t rank, world;
-  uint32_t epoch;
+  uint32_t reserved0;
   int32_t max_tiles;         /* capacity of the flag area, >= b200attn_oproj_allreduce_tiles(T, N) */
   void* staging_peers[B200_MAX_WORLD];
   void* out_peers[B200_MAX_WORLD];
   void* flags_peers[B200_MAX_WORLD];
   void* staging_mc;
   void* out_mc;
+  int64_t staging_bytes;     /* bytes of ONE staging buffer; the staging area holds two (alternating by launch) */
+  int32_t mode;              /* B200_OAR_AUTO / ONE_SHOT (every rank reduces every tile itself: shortest chain,
+                                world x the output over the fabric) / TWO_SHOT (tile owner reduces + broadcasts) */
+  void* debug_times;         /* optional uint64 [tiles][8]: %globaltimer at the epilogue's phase boundaries (tuning aid) */
 } b200_oproj_allreduce_args;
 
 int b200attn_oproj_allreduce(const b200_oproj_allreduce_args* args, b200_stream_t stream);

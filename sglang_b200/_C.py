@@ -108,15 +108,16 @@ class MergeStateArgs(C.Structure):
 
 
 MAX_WORLD = 8
+OAR_AUTO, OAR_ONE_SHOT, OAR_TWO_SHOT = 0, 1, 2
 
 
 class OProjAllReduceArgs(C.Structure):
     _fields_ = [
         ("x", vp), ("w", vp), ("x_stride", i64), ("w_stride", i64),
         ("num_tokens", i32), ("out_features", i32), ("in_features", i32), ("dtype", i32),
-        ("rank", i32), ("world", i32), ("epoch", C.c_uint32), ("max_tiles", i32),
+        ("rank", i32), ("world", i32), ("reserved0", C.c_uint32), ("max_tiles", i32),
         ("staging_peers", vp * MAX_WORLD), ("out_peers", vp * MAX_WORLD), ("flags_peers", vp * MAX_WORLD),
-        ("staging_mc", vp), ("out_mc", vp),
+        ("staging_mc", vp), ("out_mc", vp), ("staging_bytes", i64), ("mode", i32), ("debug_times", vp),
     ]
 
 

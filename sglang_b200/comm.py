@@ -30,10 +30,11 @@ def num_tiles(num_tokens: int, out_features: int) -> int:
 
 
 def symmetric_layout(max_tokens: int, out_features: int, itemsize: int, max_tiles: int):
-    """Byte offsets of the three regions inside the one symmetric allocation: staging | out | flags."""
+    """Byte offsets of the regions inside the one symmetric allocation: staging x 2 | out | flags."""
     region = (max_tokens * out_features * itemsize + 1023) // 1024 * 1024
-    flag_bytes = (max_tiles * (_C.MAX_WORLD + 1) * 4 + 1023) // 1024 * 1024
-    return {"staging": 0, "out": region, "flags": 2 * region, "total": 2 * region + flag_bytes}
+    flag_bytes = (int(_C.lib.b200attn_oproj_allreduce_flag_words(max_tiles)) * 4 + 1023) // 1024 * 1024
+    return {"staging": 0, "staging_bytes": region, "out": 2 * region, "flags": 3 * region,
+            "total": 3 * region + flag_bytes}
 
 
 class OProjAllReduce:
@@ -43,7 +44,7 @@ class OProjAllReduce:
     reference's custom all-reduce returns its registered buffer."""
 
     def __init__(self, group, max_tokens: int, out_features: int, dtype: torch.dtype, device,
-                 use_multicast: bool = True):
+                 use_multicast: bool = True, mode: int = _C.OAR_AUTO):
         import torch.distributed as dist
 
         self.group = group
@@ -61,9 +62,11 @@ class OProjAllReduce:
         if self.device.type != "cuda":
             raise RuntimeError("OProjAllReduce needs a CUDA device (sm_100a); there is no CPU fallback")
         self.max_tiles = num_tiles(self.max_tokens, self.N)
-        self.epoch = 0
         self.lay = symmetric_layout(self.max_tokens, self.N, dtype.itemsize, self.max_tiles)
+        self.mode = mode
         self._mc = 0
+        #: optional int64 [max_tiles, 8] tensor the kernel fills with %globaltimer stamps (tuning aid)
+        self.debug_times: Optional[torch.Tensor] = None
         if self.world == 1:
             self._buf = torch.zeros(self.lay["total"], dtype=torch.uint8, device=self.device)
             self._peer_ptrs: List[int] = [self._buf.data_ptr()]
@@ -75,7 +78,7 @@ class OProjAllReduce:
             self._peer_ptrs = [int(p) for p in self._hdl.buffer_ptrs]
             if use_multicast:
                 self._mc = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
-            self._buf.zero_()                       # flags start at 0; epochs count from 1
+            self._buf.zero_()                       # flags and the device-side launch counter start at 0
             torch.cuda.synchronize(self.device)
             dist.barrier(group)
         lo = self.lay["out"]
@@ -99,13 +102,14 @@ class OProjAllReduce:
             raise ValueError(f"{T} tokens exceed the communicator's capacity {self.max_tokens}")
         if T == 0:
             return self._out[:0]
-        self.epoch = self.epoch % 0xFFFFFFF0 + 1
         a = _C.OProjAllReduceArgs(
             x=x.data_ptr(), w=w.data_ptr(), x_stride=x.stride(0), w_stride=w.stride(0),
             num_tokens=T, out_features=self.N, in_features=K, dtype=ops.dtype_code(self.dtype),
-            rank=self.rank, world=self.world, epoch=self.epoch, max_tiles=self.max_tiles,
+            rank=self.rank, world=self.world, max_tiles=self.max_tiles,
             staging_mc=(self._mc + self.lay["staging"]) if self._mc else None,
             out_mc=(self._mc + self.lay["out"]) if self._mc else None,
+            staging_bytes=self.lay["staging_bytes"], mode=self.mode,
+            debug_times=self.debug_times.data_ptr() if self.debug_times is not None else None,
         )
         for r, base in enumerate(self._peer_ptrs):
             a.staging_peers[r] = base + self.lay["staging"]

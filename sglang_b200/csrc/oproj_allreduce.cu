@@ -31,19 +31,25 @@ namespace b200 {
 namespace {
 namespace oar {
 
-constexpr int BM = 128, BN = 64, BK = 64;          // BK * 2 bytes = one 128-byte swizzle row
-constexpr int kStages = 6;
-constexpr int kATile = BM * BK * 2, kBTile = BN * BK * 2, kStageBytes = kATile + kBTile;
+constexpr int BM = 128, BN = 64, BK = 128;         // BK * 2 bytes = two 128-byte swizzle rows per tile row
+// Ring of up to kMaxStages k-blocks.  The w tiles (16 KiB each) sit back to back; the x tiles are packed at
+// a_rows * 256 bytes each, a_rows = min(T, 128) rounded up to 8: the MMA still reads 128 rows from a swizzle
+// block's base, i.e. it runs on into the following x rows (or the 32 KiB tail), which only produces output rows
+// >= T that nobody stores (MMA rows are independent).  A decode batch of 64 tokens gets 5 stages = 80 KiB of w
+// in flight per SM (128-token batches: 4).
+constexpr int kMaxStages = 12;
+constexpr int kATile = BM * BK * 2, kBTile = BN * BK * 2;
+constexpr int kSmemBudget = 227 * 1024 - 1024 /*align*/ - 512 /*barriers*/;
 constexpr int kEpiWarps = 4, kMmaWarp = 4, kProdWarp0 = 5, kProdWarps = 4;
 constexpr int kProdThreads = kProdWarps * 32;
 constexpr int kThreads = (kProdWarp0 + kProdWarps) * 32;   // 288
-constexpr int kSmemBar = kStages * kStageBytes;
-constexpr int kSmemBytes = kSmemBar + 256 + 1024;
 constexpr int kTmemCols = 64;
 constexpr int kMaxWorld = 8;
+constexpr int kExBatch = 4;            // tile pieces a thread keeps in flight during the exchange
 // barrier slots
-constexpr int kBarFull = 0, kBarEmpty = kStages, kBarAccFull = 2 * kStages, kBarAccEmpty = 2 * kStages + 1;
-constexpr int kNumBars = 2 * kStages + 2;
+constexpr int kBarFull = 0, kBarEmpty = kMaxStages, kBarAccFull = 2 * kMaxStages, kBarAccEmpty = 2 * kMaxStages + 1;
+constexpr int kNumBars = 2 * kMaxStages + 2;
+static_assert(kNumBars * 8 + 8 <= 512, "barrier area");
 
 struct Params {
   const void* x;
@@ -52,15 +58,25 @@ struct Params {
   int32_t T, N, K;
   int32_t rank, world;
   int32_t tiles_m, tiles_n;
-  uint32_t epoch;
   int32_t max_tiles;
+  int32_t stages, a_rows;           // ring depth and x rows per stage (see kMaxStages)
+  int32_t one_shot;                 // 1: every rank reduces every tile itself; 0: owner reduces + broadcasts
+  int64_t staging_bytes;            // one of the two staging buffers (alternating by launch parity)
+  uint32_t* epoch_state;            // local: {epoch of the previous launch, CTAs that have finished this launch}
   uint8_t* staging_local;
   uint8_t* staging_mc;              // multicast address of the staging buffers (nullptr: peer loads)
   uint8_t* out_mc;                  // multicast address of the output buffers
   uint8_t* staging_peers[kMaxWorld];
   uint8_t* out_peers[kMaxWorld];    // out_peers[rank] is the local output
   uint32_t* flags_peers[kMaxWorld]; // per rank: arrive[max_tiles][8] then done[max_tiles]
+  unsigned long long* debug_times;  // optional [tiles][8] globaltimer stamps of the epilogue's phases
 };
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -133,8 +149,12 @@ __global__ void __launch_bounds__(oar::kThreads, 1) oproj_allreduce_kernel(const
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  auto bar = [&](int i) -> uint32_t { return smem_base + kSmemBar + 8 * i; };
-  const uint32_t tmem_slot = smem_base + kSmemBar + 8 * kNumBars;
+  const int kStages = p.stages;
+  const uint32_t a_stage = (uint32_t)p.a_rows * 256u;
+  const uint32_t smem_a = smem_base + kStages * kBTile;                  // x ring (+ 16 KiB tail) after the w ring
+  const uint32_t smem_bar = smem_a + kStages * a_stage + kATile;
+  auto bar = [&](int i) -> uint32_t { return smem_bar + 8 * i; };
+  const uint32_t tmem_slot = smem_bar + 8 * kNumBars;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -152,66 +172,87 @@ __global__ void __launch_bounds__(oar::kThreads, 1) oproj_allreduce_kernel(const
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
+  // The epoch lives in device memory so that a CUDA-graph replay (same kernel arguments) still gets a fresh one:
+  // every CTA reads it at start, the last CTA to finish bumps it.  Every rank launches the same sequence, so the
+  // epochs agree across ranks without any host involvement.
+  uint32_t epoch = 0;
+  if (p.world > 1) epoch = *reinterpret_cast<volatile uint32_t*>(p.epoch_state) + 1;
+  // Two staging buffers, alternating by launch: a rank may still be reading launch n's partials of a faster peer
+  // that has already started launch n + 1 (one-shot mode has no "done" handshake); it cannot still be reading
+  // them when that peer starts launch n + 2, because launch n + 1 needed this rank's arrive flags.
+  const int64_t stage_off = (epoch & 1u) ? p.staging_bytes : 0;
+
   const int n_tiles = p.tiles_m * p.tiles_n;
   const int n_kb = p.K / BK;
   const int64_t row_bytes = (int64_t)p.N * 2;            // staging / output rows: [T, N] in the model dtype
 
   if (warp >= kProdWarp0) {
     // ------------------------------------------------------------------ producers: x and w tiles -> smem ring
+    // A k-block is BK = 128 elements = 256 bytes per row = two 128-byte swizzle blocks side by side: 16 lanes
+    // cover one row (two whole lines of HBM per w row and k-block), 8 rows per round.
     const int pt = threadIdx.x - kProdWarp0 * 32;
-    const int chunk = pt & 7, r0 = pt >> 3;                // 8 lanes cover one 128-byte row; 16 rows per round
-    uint32_t fill = 0;
+    const int chunk = pt & 15, r0 = pt >> 4;
+    const uint32_t a_half = a_stage >> 1;                    // bytes of one swizzle block of an x tile
+    const uint32_t swz_lo = (uint32_t)(chunk & 7), blk = (uint32_t)(chunk >> 3);
+    uint32_t s = 0, round = 0;                               // ring slot and how often the ring has wrapped
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
       const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
       const int m0 = tm * BM, n0 = tn * BN;
       const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.x) + chunk * 16;
       const uint8_t* wb = reinterpret_cast<const uint8_t*>(p.w) + ((int64_t)n0 * p.w_stride) * 2 + chunk * 16;
-      for (int kb = 0; kb < n_kb; ++kb, ++fill) {
-        const uint32_t s = fill % kStages;
-        if (fill >= (uint32_t)kStages) mbar_wait(bar(kBarEmpty + s), ((fill / kStages) - 1) & 1, 10 + s);
-        const uint32_t a_dst = smem_base + s * kStageBytes, b_dst = a_dst + kATile;
+      for (int kb = 0; kb < n_kb; ++kb) {
+        if (round > 0) mbar_wait(bar(kBarEmpty + s), (round - 1) & 1, 10 + s);
+        const uint32_t a_dst = smem_a + s * a_stage + blk * a_half, b_dst = smem_base + s * kBTile + blk * (kBTile / 2);
         const int64_t koff = (int64_t)kb * BK * 2;
 #pragma unroll
-        for (int i = 0; i < BM / 16; ++i) {
-          const int row = i * 16 + r0;
-          const bool valid = m0 + row < p.T;
-          const uint8_t* src = xb + (valid ? (int64_t)(m0 + row) * p.x_stride * 2 + koff : 0);
-          cp_async16(a_dst + row * 128 + ((chunk ^ (row & 7)) << 4), src, valid);
+        for (int i = 0; i < BN / 8; ++i) {
+          const int row = i * 8 + r0;
+          cp_async16_full(b_dst + row * 128 + ((swz_lo ^ (row & 7)) << 4), wb + (int64_t)row * p.w_stride * 2 + koff);
         }
 #pragma unroll
-        for (int i = 0; i < BN / 16; ++i) {
-          const int row = i * 16 + r0;
-          cp_async16_full(b_dst + row * 128 + ((chunk ^ (row & 7)) << 4), wb + (int64_t)row * p.w_stride * 2 + koff);
+        for (int i = 0; i < BM / 8; ++i) {
+          const int row = i * 8 + r0;
+          if (row < p.a_rows) {
+            const bool valid = m0 + row < p.T;
+            const uint8_t* src = xb + (valid ? (int64_t)(m0 + row) * p.x_stride * 2 + koff : 0);
+            cp_async16(a_dst + row * 128 + ((swz_lo ^ (row & 7)) << 4), src, valid);
+          }
         }
         cp_async_mbar_arrive_noinc(bar(kBarFull + s));
+        if (++s == (uint32_t)kStages) { s = 0; ++round; }
       }
     }
     asm volatile("cp.async.wait_all;" ::: "memory");
   } else if (warp == kMmaWarp) {
     // ------------------------------------------------------------------ MMA issue (one elected lane)
+    // This warp's loop is the serial spine of the kernel (wait -> fence -> 8 MMAs -> commit per k-block): no
+    // divisions, stage and phase counted incrementally.
     constexpr int kFmt = dtype_of<T>::value == B200_BF16 ? 1 : 0;
     constexpr uint32_t idesc = umma_idesc_f16(BM, BN, kFmt, 0, 0);
     constexpr uint32_t kHi = (1024u >> 4) | (1u << 14) | (2u << 29);     // SBO 1024 B | version 1 | SWIZZLE_128B
     constexpr uint32_t kLbo = (16u >> 4) << 16;
     auto mk = [](uint32_t lo, uint32_t hi) -> uint64_t { return ((uint64_t)hi << 32) | lo; };
     const bool leader = elect_one();
-    uint32_t fill = 0, it = 0;
+    const uint32_t a_half16 = a_stage >> 5;                  // (a_stage / 2) >> 4
+    uint32_t s = 0, phase = 0, it = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       if (it > 0) {                                         // the epilogue has drained the accumulator
         mbar_wait(bar(kBarAccEmpty), (it - 1) & 1, 20);
         tc_fence_after_sync();
       }
-      for (int kb = 0; kb < n_kb; ++kb, ++fill) {
-        const uint32_t s = fill % kStages;
-        mbar_wait(bar(kBarFull + s), (fill / kStages) & 1, 30 + s);
+      for (int kb = 0; kb < n_kb; ++kb) {
+        mbar_wait(bar(kBarFull + s), phase, 30 + s);
         fence_proxy_async_smem();
         tc_fence_after_sync();
-        const uint32_t a_lo = ((smem_base + s * kStageBytes) >> 4) | kLbo;
-        const uint32_t b_lo = ((smem_base + s * kStageBytes + kATile) >> 4) | kLbo;
+        const uint32_t a_lo = ((smem_a + s * a_stage) >> 4) | kLbo;
+        const uint32_t b_lo = ((smem_base + s * kBTile) >> 4) | kLbo;
 #pragma unroll
-        for (int ks = 0; ks < BK / 16; ++ks)
-          if (leader) umma_f16_ss(tmem_base, mk(a_lo + 2 * ks, kHi), mk(b_lo + 2 * ks, kHi), idesc, (kb | ks) ? 1u : 0u);
+        for (int ks = 0; ks < BK / 16; ++ks) {
+          const uint32_t a_off = (ks >> 2) * a_half16 + (ks & 3) * 2, b_off = (ks >> 2) * (kBTile >> 5) + (ks & 3) * 2;
+          if (leader) umma_f16_ss(tmem_base, mk(a_lo + a_off, kHi), mk(b_lo + b_off, kHi), idesc, (kb | ks) ? 1u : 0u);
+        }
         if (leader) umma_commit(bar(kBarEmpty + s));
+        if (++s == (uint32_t)kStages) { s = 0; phase ^= 1u; }
       }
       if (leader) umma_commit(bar(kBarAccFull));
     }
@@ -225,7 +266,10 @@ __global__ void __launch_bounds__(oar::kThreads, 1) oproj_allreduce_kernel(const
       const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
       const int m0 = tm * BM, n0 = tn * BN;
       const int rows = min(BM, p.T - m0);
+      unsigned long long* dbg = (p.debug_times != nullptr && et == 0) ? p.debug_times + (int64_t)tile * 8 : nullptr;
+      if (dbg) dbg[0] = globaltimer_ns();
       mbar_wait(bar(kBarAccFull), it & 1, 40);
+      if (dbg) dbg[1] = globaltimer_ns();
       tc_fence_after_sync();
       uint32_t acc[2][32];
       tmem_ld32(t_addr, acc[0]);
@@ -235,7 +279,7 @@ __global__ void __launch_bounds__(oar::kThreads, 1) oproj_allreduce_kernel(const
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(kBarAccEmpty));
       // this rank's partial tile, rounded to the model dtype: straight to the output when there is no peer
-      uint8_t* dst_base = p.world == 1 ? p.out_peers[0] : p.staging_local;
+      uint8_t* dst_base = p.world == 1 ? p.out_peers[0] : p.staging_local + stage_off;
       if (et < rows) {
         uint8_t* dst = dst_base + (int64_t)(m0 + et) * row_bytes + (int64_t)n0 * 2;
 #pragma unroll
@@ -251,39 +295,99 @@ __global__ void __launch_bounds__(oar::kThreads, 1) oproj_allreduce_kernel(const
       }
       if (p.world == 1) continue;
 
+      // ---- exchange.  Ordering: every thread's staging stores -> bar.sync -> ONE release at system scope
+      // (cumulative) per flag; on the other side one acquire per flag -> bar.sync -> everybody's loads.
       const int owner = tile % p.world;
       uint32_t* my_flags = p.flags_peers[p.rank];
-      __threadfence_system();
-      epi_sync();
-      if (et == 0) st_release_sys(p.flags_peers[owner] + (int64_t)tile * kMaxWorld + p.rank, p.epoch);
-      if (owner == p.rank) {
-        if (et < p.world) wait_flag(my_flags + (int64_t)tile * kMaxWorld + et, p.epoch, 50 + et);
-        epi_sync();
-        for (int u = et; u < rows * 8; u += 128) {           // 16-byte pieces of the tile
-          const int64_t off = (int64_t)(m0 + (u >> 3)) * row_bytes + (int64_t)n0 * 2 + (u & 7) * 16;
-          if (p.staging_mc != nullptr) {
-            multimem_st_16(p.out_mc + off, multimem_ld_reduce_16<T>(p.staging_mc + off));
-          } else {
-            float2 s[4] = {{0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}};
-            for (int r = 0; r < p.world; ++r) {               // fixed rank order: every rank gets the same bits
-              const uint4 v = ld_sys_16(p.staging_peers[r] + off);
-              const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+      uint32_t* arrive = my_flags + (int64_t)tile * kMaxWorld;
+      const int n_units = rows * 8;                            // 16-byte pieces of the tile
+      auto unit_off = [&](int u) -> int64_t {
+        return (int64_t)(m0 + (u >> 3)) * row_bytes + (int64_t)n0 * 2 + (u & 7) * 16;
+      };
+      // sum of the tile piece at `off` over all ranks: in the switch, or by peer loads in rank order
+      auto peer_sum = [&](int64_t off) -> uint4 {
+        float2 acc2[4] = {{0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}};
+        uint4 v[kMaxWorld];
 #pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const float2 f = unpack2<T>(w4[i]);
-                s[i].x += f.x; s[i].y += f.y;
-              }
+        for (int r = 0; r < kMaxWorld; ++r)
+          if (r < p.world) v[r] = ld_sys_16(p.staging_peers[r] + stage_off + off);
+#pragma unroll
+        for (int r = 0; r < kMaxWorld; ++r) {
+          if (r < p.world) {
+            const uint32_t w4[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float2 f = unpack2<T>(w4[i]);
+              acc2[i].x += f.x; acc2[i].y += f.y;
             }
-            const uint4 o = make_uint4(pack2<T>(s[0].x, s[0].y), pack2<T>(s[1].x, s[1].y), pack2<T>(s[2].x, s[2].y),
-                                       pack2<T>(s[3].x, s[3].y));
-            for (int r = 0; r < p.world; ++r) st_sys_16(p.out_peers[r] + off, o);
           }
         }
-        __threadfence_system();
+        return make_uint4(pack2<T>(acc2[0].x, acc2[0].y), pack2<T>(acc2[1].x, acc2[1].y),
+                          pack2<T>(acc2[2].x, acc2[2].y), pack2<T>(acc2[3].x, acc2[3].y));
+      };
+      epi_sync();
+      if (dbg) dbg[7] = globaltimer_ns();
+      if (p.one_shot) {
+        // one-shot: every rank tells every rank, then reduces the whole tile for itself (latency-optimal)
+        if (et < p.world) st_release_sys(p.flags_peers[et] + (int64_t)tile * kMaxWorld + p.rank, epoch);
+        if (dbg) dbg[2] = globaltimer_ns();
+        if (et < p.world) wait_flag(arrive + et, epoch, 50 + et);
         epi_sync();
-        if (et < p.world) st_release_sys(p.flags_peers[et] + (int64_t)p.max_tiles * kMaxWorld + tile, p.epoch);
+        if (dbg) dbg[3] = globaltimer_ns();
+        uint8_t* out = p.out_peers[p.rank];
+        for (int u0 = et; u0 < n_units; u0 += 128 * kExBatch) {
+          uint4 v[kExBatch];
+#pragma unroll
+          for (int b = 0; b < kExBatch; ++b) {
+            const int u = u0 + b * 128;
+            if (u < n_units)
+              v[b] = p.staging_mc != nullptr ? multimem_ld_reduce_16<T>(p.staging_mc + stage_off + unit_off(u))
+                                             : peer_sum(unit_off(u));
+          }
+#pragma unroll
+          for (int b = 0; b < kExBatch; ++b) {
+            const int u = u0 + b * 128;
+            if (u < n_units) *reinterpret_cast<uint4*>(out + unit_off(u)) = v[b];
+          }
+        }
+        if (dbg) dbg[6] = globaltimer_ns();
+        continue;
       }
-      if (et == 0) wait_flag(my_flags + (int64_t)p.max_tiles * kMaxWorld + tile, p.epoch, 60);
+      // two-shot: the tile's owner reduces it and writes the result into every rank's output
+      if (et == 0) st_release_sys(p.flags_peers[owner] + (int64_t)tile * kMaxWorld + p.rank, epoch);
+      if (dbg) dbg[2] = globaltimer_ns();
+      if (owner == p.rank) {
+        if (et < p.world) wait_flag(arrive + et, epoch, 50 + et);
+        epi_sync();
+        if (dbg) dbg[3] = globaltimer_ns();
+        for (int u0 = et; u0 < n_units; u0 += 128 * kExBatch) {
+          uint4 v[kExBatch];
+#pragma unroll
+          for (int b = 0; b < kExBatch; ++b) {
+            const int u = u0 + b * 128;
+            if (u < n_units)
+              v[b] = p.staging_mc != nullptr ? multimem_ld_reduce_16<T>(p.staging_mc + stage_off + unit_off(u))
+                                             : peer_sum(unit_off(u));
+          }
+#pragma unroll
+          for (int b = 0; b < kExBatch; ++b) {
+            const int u = u0 + b * 128;
+            if (u < n_units) {
+              if (p.staging_mc != nullptr) {
+                multimem_st_16(p.out_mc + unit_off(u), v[b]);
+              } else {
+                for (int r = 0; r < p.world; ++r) st_sys_16(p.out_peers[r] + unit_off(u), v[b]);
+              }
+            }
+          }
+        }
+        if (dbg) dbg[4] = globaltimer_ns();
+        epi_sync();
+        if (dbg) dbg[5] = globaltimer_ns();
+        if (et < p.world) st_release_sys(p.flags_peers[et] + (int64_t)p.max_tiles * kMaxWorld + tile, epoch);
+      }
+      if (et == 0) wait_flag(my_flags + (int64_t)p.max_tiles * kMaxWorld + tile, epoch, 60);
+      if (dbg) dbg[6] = globaltimer_ns();
       epi_sync();
     }
   }
@@ -292,6 +396,14 @@ __global__ void __launch_bounds__(oar::kThreads, 1) oproj_allreduce_kernel(const
   if (warp == kMmaWarp) {
     tc_fence_after_sync();
     tmem_dealloc<kTmemCols>(tmem_base);
+  }
+  if (p.world > 1 && threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(p.epoch_state + 1, 1u) == gridDim.x - 1) {   // last CTA of this launch
+      p.epoch_state[1] = 0;
+      __threadfence();
+      *reinterpret_cast<volatile uint32_t*>(p.epoch_state) = epoch;
+    }
   }
 }
 
@@ -308,7 +420,7 @@ bool oar_mc_enabled() {
 }  // namespace b200
 
 extern "C" int64_t b200attn_oproj_allreduce_flag_words(int32_t max_tiles) {
-  return (int64_t)max_tiles * (b200::oar::kMaxWorld + 1);
+  return (int64_t)max_tiles * (b200::oar::kMaxWorld + 1) + 2;   // arrive | done | {epoch, exit counter}
 }
 
 extern "C" int32_t b200attn_oproj_allreduce_tiles(int32_t T, int32_t N) {
@@ -325,7 +437,7 @@ extern "C" int b200attn_oproj_allreduce(const b200_oproj_allreduce_args* a, b200
   B200_CHECK_ARG(a->dtype == B200_BF16 || a->dtype == B200_F16, "oproj_allreduce: dtype %d", a->dtype);
   B200_CHECK_ARG(a->num_tokens > 0 && a->out_features > 0 && a->in_features > 0 && a->out_features % BN == 0 &&
                      a->in_features % BK == 0,
-                 "oproj_allreduce: T=%d N=%d K=%d (N and K must be multiples of 64)", a->num_tokens, a->out_features,
+                 "oproj_allreduce: T=%d N=%d K=%d (N must be a multiple of 64, K of 128)", a->num_tokens, a->out_features,
                  a->in_features);
   B200_CHECK_ARG(a->world >= 1 && a->world <= kMaxWorld && a->rank >= 0 && a->rank < a->world,
                  "oproj_allreduce: rank %d / world %d", a->rank, a->world);
@@ -337,7 +449,9 @@ extern "C" int b200attn_oproj_allreduce(const b200_oproj_allreduce_args* a, b200
   p.T = a->num_tokens; p.N = a->out_features; p.K = a->in_features;
   p.rank = a->rank; p.world = a->world;
   p.tiles_m = (p.T + BM - 1) / BM; p.tiles_n = p.N / BN;
-  p.epoch = a->epoch; p.max_tiles = a->max_tiles;
+  p.max_tiles = a->max_tiles; p.epoch_state = nullptr; p.one_shot = 0;
+  p.staging_bytes = a->staging_bytes;
+  p.debug_times = reinterpret_cast<unsigned long long*>(a->debug_times);
   const int n_tiles = p.tiles_m * p.tiles_n;
   for (int r = 0; r < kMaxWorld; ++r) {
     p.staging_peers[r] = nullptr; p.out_peers[r] = nullptr; p.flags_peers[r] = nullptr;
@@ -348,7 +462,6 @@ extern "C" int b200attn_oproj_allreduce(const b200_oproj_allreduce_args* a, b200
     p.staging_local = nullptr; p.staging_mc = nullptr; p.out_mc = nullptr;
   } else {
     B200_CHECK_ARG(n_tiles <= a->max_tiles, "oproj_allreduce: %d tiles exceed the flag area (%d)", n_tiles, a->max_tiles);
-    B200_CHECK_ARG(a->epoch != 0, "oproj_allreduce: epoch must be non-zero (flags start at 0)");
     for (int r = 0; r < a->world; ++r) {
       B200_CHECK_ARG(a->staging_peers[r] && a->out_peers[r] && a->flags_peers[r] && a16(a->staging_peers[r]) &&
                          a16(a->out_peers[r]),
@@ -358,29 +471,50 @@ extern "C" int b200attn_oproj_allreduce(const b200_oproj_allreduce_args* a, b200
       p.flags_peers[r] = reinterpret_cast<uint32_t*>(a->flags_peers[r]);
     }
     p.staging_local = p.staging_peers[a->rank];
+    B200_CHECK_ARG(a->staging_bytes >= (int64_t)a->num_tokens * a->out_features * 2 && a->staging_bytes % 16 == 0,
+                   "oproj_allreduce: staging_bytes %lld too small for [%d, %d]", (long long)a->staging_bytes,
+                   a->num_tokens, a->out_features);
+    // one-shot moves world x the output through the fabric but has the shorter dependency chain: use it while
+    // the whole exchange stays small (decode batches); B200_OAR_* force a mode
+    const int64_t fabric_bytes = (int64_t)a->num_tokens * a->out_features * 2 * a->world;
+    // measured on 8 x B200 (profiles/r1_oproj_allreduce_tp8.json): hidden 8192, T = 32 one-shot 21 us / two-shot
+    // 23 us, T = 64: 27 / 24 us; with two ranks both modes move the same bytes and one-shot always wins
+    p.one_shot = a->mode == B200_OAR_ONE_SHOT ||
+                 (a->mode == B200_OAR_AUTO && (a->world <= 2 || fabric_bytes <= (int64_t)(4 << 20)));
+    p.epoch_state = p.flags_peers[a->rank] + (int64_t)a->max_tiles * (kMaxWorld + 1);
     const bool mc = oar_mc_enabled() && a->staging_mc != nullptr && a->out_mc != nullptr;
     p.staging_mc = mc ? reinterpret_cast<uint8_t*>(a->staging_mc) : nullptr;
     p.out_mc = mc ? reinterpret_cast<uint8_t*>(a->out_mc) : nullptr;
   }
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  p.a_rows = ((p.T < BM ? p.T : BM) + 7) / 8 * 8;
+  p.stages = (kSmemBudget - kATile) / (kBTile + p.a_rows * 256);
+  if (p.stages > kMaxStages) p.stages = kMaxStages;
+  {
+    static int cap = -1;                                   // B200ATTN_OAR_STAGES: tuning aid
+    if (cap < 0) { const char* e = getenv("B200ATTN_OAR_STAGES"); cap = e ? atoi(e) : 0; }
+    if (cap >= 2 && cap < p.stages) p.stages = cap;
+  }
+  const int smem_bytes = p.stages * (kBTile + p.a_rows * 256) + kATile + 512 + 1024;
+  const int kSmemMax = 227 * 1024;
   const int grid = n_tiles < sm_count() ? n_tiles : sm_count();   // every CTA resident: peers wait on each other
   B200_CHECK_ARG(grid > 0, "oproj_allreduce: no SMs?");
   if (a->dtype == B200_BF16) {
     static bool configured = false;
     auto kern = oproj_allreduce_kernel<__nv_bfloat16>;
     if (!configured) {
-      B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+      B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax));
       configured = true;
     }
-    kern<<<grid, kThreads, kSmemBytes, stream>>>(p);
+    kern<<<grid, kThreads, smem_bytes, stream>>>(p);
   } else {
     static bool configured = false;
     auto kern = oproj_allreduce_kernel<__half>;
     if (!configured) {
-      B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+      B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax));
       configured = true;
     }
-    kern<<<grid, kThreads, kSmemBytes, stream>>>(p);
+    kern<<<grid, kThreads, smem_bytes, stream>>>(p);
   }
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;

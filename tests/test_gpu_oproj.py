@@ -8,8 +8,8 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-@pytest.mark.parametrize("T,N,K", [(1, 64, 64), (64, 4096, 4096), (37, 8192, 1024), (128, 512, 8192),
-                                   (129, 256, 192), (300, 19 * 64, 320), (1000, 4096, 512)])
+@pytest.mark.parametrize("T,N,K", [(1, 64, 128), (64, 4096, 4096), (37, 8192, 1024), (128, 512, 8192),
+                                   (129, 256, 384), (300, 19 * 64, 640), (1000, 4096, 512)])
 def test_oproj_single_gpu_matches_fp64(T, N, K, dtype):
     from sglang_b200.comm import OProjAllReduce, oproj_allreduce_ref
 
@@ -44,6 +44,6 @@ def test_oproj_rejects_bad_shapes():
     x = torch.zeros(4, 96, dtype=torch.bfloat16, device="cuda")
     w = torch.zeros(128, 96, dtype=torch.bfloat16, device="cuda")
     with pytest.raises(_C.B200AttnError):
-        comm.forward(x, w)                       # K must be a multiple of 64
+        comm.forward(x, w)                       # K must be a multiple of 128
     with pytest.raises(RuntimeError):
         comm.forward(x.cpu(), w.cpu())

@@ -127,3 +127,62 @@ def test_two_rank_head_sharding_needs_no_collective():
         p.join(timeout=180)
         assert p.exitcode == 0
     assert ret.get(timeout=10) is True
+
+
+# ----------------------------------------------------------------------------- o_proj + all-reduce host logic (8f-4)
+def test_oproj_tile_plan_and_symmetric_layout():
+    from sglang_b200 import _C
+    from sglang_b200.comm import num_tiles, symmetric_layout, tile_owner
+
+    assert num_tiles(64, 8192) == 128 and num_tiles(129, 8192) == 256 and num_tiles(1, 64) == 1
+    assert num_tiles(64, 8192) == _C.lib.b200attn_oproj_allreduce_tiles(64, 8192)
+    assert [tile_owner(t, 8) for t in range(10)] == [0, 1, 2, 3, 4, 5, 6, 7, 0, 1]
+    lay = symmetric_layout(128, 8192, 2, num_tiles(128, 8192))
+    one = 128 * 8192 * 2
+    # two staging buffers (alternating by launch), the output, the flag area; 1 KiB-aligned regions, no overlap
+    assert lay["staging"] == 0 and lay["staging_bytes"] >= one and lay["out"] >= 2 * lay["staging_bytes"]
+    assert lay["flags"] >= lay["out"] + one and lay["total"] >= lay["flags"] + 4 * _C.lib.b200attn_oproj_allreduce_flag_words(128)
+    assert all(v % 1024 == 0 for v in lay.values())
+    assert _C.lib.b200attn_oproj_allreduce_flag_words(128) == 128 * 9 + 2
+
+
+def _oproj_worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from sglang_b200.comm import oproj_allreduce_ref
+
+        g = torch.Generator().manual_seed(3)
+        T, N, K = 9, 64, 128 * world
+        x = torch.randn(T, K, generator=g).bfloat16()            # the attention output, all heads
+        w = torch.randn(N, K, generator=g).bfloat16()            # o_proj weight [hidden, Hq * D]
+        ks = K // world
+        xs = [x[:, r * ks : (r + 1) * ks] for r in range(world)]  # RowParallelLinear: input split along K
+        ws = [w[:, r * ks : (r + 1) * ks] for r in range(world)]
+        # the reference's data flow on this rank: local GEMM in the model dtype, then all-reduce
+        part = (xs[rank].double() @ ws[rank].double().t()).float().bfloat16().float()
+        dist.all_reduce(part)                                      # gloo sums in float32, rank order 0 + 1
+        want = oproj_allreduce_ref(xs, ws)
+        ok = torch.equal(part.bfloat16(), want)
+        # and the sharded sum approximates the unsharded projection
+        full = (x.double() @ w.double().t()).float()
+        ok = ok and float((want.float() - full).abs().max()) <= 2.0 ** -7 * float(full.abs().max()) * 2
+        if rank == 0:
+            ret.put(bool(ok))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_oproj_allreduce_reference_flow():
+    """world_size 2 over gloo: the definition the fused kernel is held to (per-rank partial in the model dtype,
+    fp32 sum, one rounding) equals RowParallelLinear + all-reduce as the reference runs it."""
+    ctx = mp.get_context("spawn")
+    ret = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_oproj_worker, args=(r, 2, port, ret)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=180)
+        assert p.exitcode == 0
+    assert ret.get(timeout=10) is True
