@@ -61,6 +61,49 @@ __global__ void rate_kernel(long long* out, uint32_t* sink, uint32_t seed) {
         asm volatile("mma.sync.aligned.m16n8k32.row.col.f32.e4m3.e4m3.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                      : "+f"(f[i][0]), "+f"(f[i][1]), "+f"(f[i][2]), "+f"(f[i][3])
                      : "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4 + (i & 3)]), "r"(r[8 + (i & 3)]));
+    } else if constexpr (OP == 9) {  // 8 packed-half exp2 (two results per lane)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) asm volatile("ex2.approx.f16x2 %0, %0;" : "+r"(r[i]));
+    } else if constexpr (OP == 10) {  // 8 packed-bf16 exp2
+#pragma unroll
+      for (int i = 0; i < 8; ++i) asm volatile("ex2.approx.ftz.bf16x2 %0, %0;" : "+r"(r[i]));
+    } else if constexpr (OP == 11) {  // 8 FFMA2 (fma.rn.f32x2)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        uint64_t a, b;
+        asm volatile("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(f[i][0]), "f"(f[i][1]));
+        asm volatile("mov.b64 %0, {%1, %2};" : "=l"(b) : "f"(f[i][2]), "f"(f[i][3]));
+        asm volatile("fma.rn.f32x2 %0, %0, %1, %1;" : "+l"(a) : "l"(b));
+        asm volatile("mov.b64 {%0, %1}, %2;" : "=f"(f[i][0]), "=f"(f[i][1]) : "l"(a));
+      }
+    } else if constexpr (OP == 12) {  // 8 FADD2 (add.rn.f32x2)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        uint64_t a, b;
+        asm volatile("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(f[i][0]), "f"(f[i][1]));
+        asm volatile("mov.b64 %0, {%1, %2};" : "=l"(b) : "f"(f[i][2]), "f"(f[i][3]));
+        asm volatile("add.rn.f32x2 %0, %0, %1;" : "+l"(a) : "l"(b));
+        asm volatile("mov.b64 {%0, %1}, %2;" : "=f"(f[i][0]), "=f"(f[i][1]) : "l"(a));
+      }
+    } else if constexpr (OP == 13) {  // 8 F2FP f32,f32 -> bf16x2
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r[8 + i]) : "f"(f[i][0]), "f"(f[i][1]));
+        f[i][0] += 1.f;   // FADD keeps the chain alive (counted below as one of two instructions)
+      }
+    } else if constexpr (OP == 14) {  // 8 FMNMX3
+#pragma unroll
+      for (int i = 0; i < 8; ++i) asm volatile("max.f32 %0, %0, %1, %2;" : "+f"(f[i][0]) : "f"(f[i][1]), "f"(f[i][2]));
+    } else if constexpr (OP == 15) {  // 8 FFMA
+#pragma unroll
+      for (int i = 0; i < 8; ++i) asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(f[i][0]) : "f"(f[i][1]), "f"(f[i][2]));
+    } else if constexpr (OP == 16) {  // 8 F2FP f32,f32 -> f16x2 feeding 8 packed-half exp2
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        asm volatile("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r[i]) : "f"(f[i][0]), "f"(f[i][1]));
+        asm volatile("ex2.approx.f16x2 %0, %0;" : "+r"(r[i]));
+        f[i][0] = __uint_as_float(r[i]);
+      }
     } else if constexpr (OP == 8) {  // 8 IMAD (shift-left stand-in)
 #pragma unroll
       for (int i = 0; i < 8; ++i) asm volatile("mad.lo.u32 %0, %0, 256, %1;" : "+r"(r[i]) : "r"(r[8 + i]));
@@ -103,5 +146,13 @@ int main() {
   run<6>("PRMT", 8, out);
   run<4>("LDSM.x4", 4, out);
   run<5>("MUFU.EX2", 8, out);
+  run<9>("MUFU.EX2 f16x2", 8, out);
+  run<10>("MUFU.EX2 bf16x2", 8, out);
+  run<11>("FFMA2 (fma.rn.f32x2)", 8, out);
+  run<12>("FADD2 (add.rn.f32x2)", 8, out);
+  run<15>("FFMA", 8, out);
+  run<14>("FMNMX3", 8, out);
+  run<13>("F2FP bf16x2 + FADD", 16, out);
+  run<16>("F2FP f16x2 + EX2 f16x2", 16, out);
   return 0;
 }

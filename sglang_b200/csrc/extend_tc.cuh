@@ -25,6 +25,14 @@
 // Shared memory: Q0,Q1 32 KiB each | ring of 5 x 32 KiB slots filled K0 V0 K1 V1 ... | barriers.
 
 
+// Timing-aid ablations (never defined in the shipped build): skip the ring refills / the exponentials.
+#ifndef B200_ABLATE_FILL
+#define B200_ABLATE_FILL 0
+#endif
+#ifndef B200_ABLATE_EXP
+#define B200_ABLATE_EXP 0
+#endif
+
 namespace {
 namespace tc {
 
