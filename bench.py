@@ -57,6 +57,8 @@ def parse_args():
     ap.add_argument("--no-secondary", action="store_true",
                     help="skip the one-layer cfg3 (FP8 decode) / cfg5 (prefix-reuse extend) / KV-store side measurements")
     ap.add_argument("--kernel", default="auto", choices=["auto", "generic"])
+    ap.add_argument("--no-graph", action="store_true",
+                    help="time eager launches instead of replaying the step as one CUDA graph")
     return ap.parse_args()
 
 
@@ -273,9 +275,39 @@ def run_ours(args):
 
     for _ in range(max(args.warmup, 3)):
         step()
+
+    # ---- the step as the serving engine runs it: one CUDA graph of the whole 32-layer decode step, replayed after
+    # the backend's replay prep (decode_cuda_graph_runner.py:946-953 capture, :1168 replay)
+    graph, per_graph = None, 0
+    if not args.no_graph:
+        backend.init_cuda_graph_state(bs, bs)
+        side = torch.cuda.Stream(device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            step()                                   # warm-up on the capture stream with the graph-state workspaces
+            graph = torch.cuda.CUDAGraph()
+            backend.init_forward_metadata_out_graph(fb, in_capture=True)
+            n_cap = ops.launch_count
+            graph_outs = []
+            with torch.cuda.graph(graph, stream=side):
+                backend.init_forward_metadata_in_graph(fb)
+                for l in range(layers):
+                    q, k, v = split_qkv(qkv[l], cfg)
+                    graph_outs.append(backend.forward_decode(q, k, v, layer_objs[l], fb))
+            per_graph = ops.launch_count - n_cap
+        torch.cuda.current_stream().wait_stream(side)
+
+        def graph_step():
+            backend.init_forward_metadata_out_graph(fb)
+            graph.replay()
+
+        for _ in range(3):
+            graph_step()
+
     # live per-kernel timing: one event pair per (step, layer) around the decode attention kernel
+    ev_steps = args.steps if graph is None else min(args.steps, 20)
     pairs = [[(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(layers)]
-             for _ in range(args.steps)]
+             for _ in range(ev_steps)]
     for s_ in pairs:
         for a, b in s_:
             a.record(); b.record()
@@ -285,17 +317,24 @@ def run_ours(args):
         time.sleep(0.15)
     barrier()
     n0 = ops.launch_count
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0, ev1, ev2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
     t0 = time.perf_counter()
     ev0.record()
-    for s in range(args.steps):
-        step(pairs[s])
+    if graph is not None:
+        for s in range(args.steps):
+            graph_step()
     ev1.record()
+    # eager launches of the same step with CUDA events around every attention(+merge) launch: the whole timed
+    # region when --no-graph, else a shorter instrumented pass (events cannot bracket kernels inside a replay)
+    for s in range(ev_steps):
+        step(pairs[s])
+    ev2.record()
     barrier()
     t1 = time.perf_counter()
-    launches = ops.launch_count - n0
+    launches = ops.launch_count - n0 + (per_graph * args.steps if graph is not None else 0)
     clocks = sampler.stop(t0, t1) if rank == 0 else None
-    ms = ev0.elapsed_time(ev1) / args.steps
+    eager_ms = ev1.elapsed_time(ev2) / ev_steps
+    ms = ev0.elapsed_time(ev1) / args.steps if graph is not None else eager_ms
     kern_ms = sorted(a.elapsed_time(b) for s_ in pairs for a, b in s_)
     kern_avg = sum(kern_ms) / len(kern_ms)
 
@@ -307,17 +346,68 @@ def run_ours(args):
     d_meta = torch.empty_like(h_meta, device=device)
     from sglang_b200.srt_mirror import ForwardBatch, ForwardMode
 
+    # Copies run on their own streams so that the PCIe transfers of the next layers' inputs and the previous layers'
+    # outputs overlap the kernels; every byte still crosses inside the timed region, every step, and the step ends
+    # when the last output byte is on the host.  With graphs the step is cut into segments of `seg` layers, one
+    # CUDA graph each (driving 96 launches + 64 copies per step from Python is CPU-bound otherwise).
+    s_in, s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
+    seg = 4 if (graph is not None and layers % 4 == 0) else 1
+    n_seg = layers // seg
+    in_ev = [torch.cuda.Event() for _ in range(n_seg)]
+    done_ev = [torch.cuda.Event() for _ in range(n_seg)]
+    seg_graphs, seg_outs = [], []
+    if graph is not None:
+        side = torch.cuda.Stream(device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            backend.init_forward_metadata_out_graph(fb, in_capture=True)
+            for i in range(n_seg):
+                g_i, outs = torch.cuda.CUDAGraph(), []
+                with torch.cuda.graph(g_i, stream=side):
+                    if i == 0:
+                        backend.init_forward_metadata_in_graph(fb)
+                    for l in range(i * seg, (i + 1) * seg):
+                        q, k, v = split_qkv(qkv[l], cfg)
+                        outs.append(backend.forward_decode(q, k, v, layer_objs[l], fb))
+                    out_i = torch.stack(outs)            # one D2H copy per segment
+                seg_graphs.append(g_i)
+                seg_outs.append(out_i)
+        torch.cuda.current_stream().wait_stream(side)
+
     def e2e_step():
-        qkv.copy_(h_qkv, non_blocking=True)
-        d_meta.copy_(h_meta, non_blocking=True)
-        fb2 = ForwardBatch(forward_mode=ForwardMode.DECODE, batch_size=bs, req_pool_indices=d_meta[0],
-                           seq_lens=d_meta[1], out_cache_loc=d_meta[2], seq_lens_sum=bs * cfg["ctx"])
-        backend.init_forward_metadata(fb2)
-        for l in range(layers):
-            q, k, v = split_qkv(qkv[l], cfg)
-            o = backend.forward_decode(q, k, v, layer_objs[l], fb2)
-            h_out[l].copy_(o, non_blocking=True)
-        torch.cuda.current_stream().synchronize()   # the caller reads the result
+        cur = torch.cuda.current_stream()
+        s_in.wait_stream(cur)                      # previous step's readers of qkv are done (the step ends in a sync)
+        with torch.cuda.stream(s_in):
+            for i in range(n_seg):
+                qkv[i * seg:(i + 1) * seg].copy_(h_qkv[i * seg:(i + 1) * seg], non_blocking=True)
+                in_ev[i].record(s_in)
+        if graph is not None:
+            # the runner's static metadata buffers are refreshed from the host, then the replay prep
+            fb.req_pool_indices.copy_(h_meta[0], non_blocking=True)
+            fb.seq_lens.copy_(h_meta[1], non_blocking=True)
+            fb.out_cache_loc.copy_(h_meta[2], non_blocking=True)
+            backend.init_forward_metadata_out_graph(fb)
+            fb2 = fb
+        else:
+            d_meta.copy_(h_meta, non_blocking=True)
+            fb2 = ForwardBatch(forward_mode=ForwardMode.DECODE, batch_size=bs, req_pool_indices=d_meta[0],
+                               seq_lens=d_meta[1], out_cache_loc=d_meta[2], seq_lens_sum=bs * cfg["ctx"])
+            backend.init_forward_metadata(fb2)
+        for i in range(n_seg):
+            cur.wait_event(in_ev[i])
+            if graph is not None:
+                seg_graphs[i].replay()
+                o = seg_outs[i]
+            else:
+                q, k, v = split_qkv(qkv[i], cfg)
+                o = backend.forward_decode(q, k, v, layer_objs[i], fb2).unsqueeze(0)
+                o.record_stream(s_out)
+            done_ev[i].record(cur)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(done_ev[i])
+                h_out[i * seg:(i + 1) * seg].copy_(o.view(seg, bs, -1), non_blocking=True)
+        s_out.synchronize()                        # the caller reads the result
+        cur.synchronize()
 
     for _ in range(3):
         e2e_step()
@@ -328,13 +418,20 @@ def run_ours(args):
         e2e_step()
     barrier()
     e2e_ms = (time.perf_counter() - te0) / e2e_steps * 1e3
+    # the bytes that reached the host are the attention outputs of the inputs that were copied in
+    for l in (0, layers - 1):
+        q, k, v = split_qkv(qkv[l], cfg)
+        want = backend.forward_decode(q, k, v, layer_objs[l], fb).float().cpu()
+        err = float((h_out[l].float() - want.view_as(h_out[l])).abs().max())
+        if not err <= 2e-2:
+            raise RuntimeError(f"e2e output of layer {l} differs from the device-side result by {err}")
     h2d = h_qkv.numel() * 2 + h_meta.numel() * 8
     d2h = h_out.numel() * 2
 
-    t = torch.tensor([ms, e2e_ms, kern_avg], dtype=torch.float64, device=device)
+    t = torch.tensor([ms, e2e_ms, kern_avg, eager_ms], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, e2e_ms, kern_avg = (float(x) for x in t.cpu())
+    ms, e2e_ms, kern_avg, eager_ms = (float(x) for x in t.cpu())
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -360,13 +457,18 @@ def run_ours(args):
         "config": {"workload": "llama-3.1-8b decode attention, bs 64 @ 4096 ctx, page_size 1 (BASELINE cfg2)",
                    "layers": layers, "heads_per_gpu": [Hq, Hkv], "head_dim": D, "parallelism": f"tp{world}-head-shards",
                    "l2": "inputs larger than L2 (1.07 GB of KV per layer vs 126 MB L2); no flush",
-                   "decode_kernel": args.kernel},
+                   "decode_kernel": args.kernel,
+                   "launch": ("one CUDA graph of the whole step, replayed after init_forward_metadata_out_graph "
+                              "(how SGLang's decode runner drives a backend)" if graph is not None else "eager launches")},
+        "ms_per_step_eager": round(eager_ms, 4),
         "tokens_per_s": round(bs * world / (ms * 1e-3), 1),
         "pct_of_8TBs": round(100 * value / world / 8000.0, 2),
         "roofline": {"bound": "hbm", "kernel": "decode_hg_kernel<128,bf16> + decode_merge_fast_kernel", "achieved": round(achieved, 1), "peak": peak,
                      "peak_source": peak_src, "unit": "GB/s", "frac": round(achieved / peak, 4),
                      "frac_of_8TBs_nominal": round(achieved / 8000.0, 4), "kernel_us_avg": round(kern_avg * 1e3, 2),
-                     "kernel_us_median": round(kern_ms[len(kern_ms) // 2] * 1e3, 2), "traffic": traffic},
+                     "kernel_us_median": round(kern_ms[len(kern_ms) // 2] * 1e3, 2), "traffic": traffic,
+                     "timing": f"CUDA events around each attention+merge launch pair, {ev_steps} eager steps x {layers} "
+                               "layers inside the timed run"},
         "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "ms_per_step": round(e2e_ms, 4),
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches,
