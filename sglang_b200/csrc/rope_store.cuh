@@ -257,7 +257,9 @@ struct RopeFastParams {
 constexpr int kRopeBatch = 4;
 constexpr int kRopeWarps = 4;
 
-template <typename SRC, typename DST, int D, bool NEOX>
+// SCALED = false: k_scale == v_scale == 1 (no IEEE divisions compiled in: 128 inlined div.rn sequences made the FP8
+// instance 5 000+ instructions long and instruction-fetch bound).
+template <typename SRC, typename DST, int D, bool NEOX, bool SCALED>
 __global__ void __launch_bounds__(kRopeWarps * 32) rope_store_fast_kernel(const RopeFastParams fp) {
   constexpr int TPH = D / 16, HPP = 32 / TPH;
   const RopeParams& p = fp.b;
@@ -329,7 +331,7 @@ __global__ void __launch_bounds__(kRopeWarps * 32) rope_store_fast_kernel(const 
   const SRC* vrow = reinterpret_cast<const SRC*>(p.v) + token * p.v_stride_t;
   DST* kdst = store ? reinterpret_cast<DST*>(p.k_cache) + slot * p.k_cache_stride : nullptr;
   DST* vdst = store ? reinterpret_cast<DST*>(p.v_cache) + slot * p.v_cache_stride : nullptr;
-  const bool k_scaled = p.k_scale != 1.0f, v_scaled = p.v_scale != 1.0f;
+  const bool k_scaled = SCALED && p.k_scale != 1.0f, v_scaled = SCALED && p.v_scale != 1.0f;
   const int v_chunks = p.Hkv * (D / 8);                       // 16-byte chunks of the token's V row
 
   for (int p0 = p_begin; p0 < p_end; p0 += kRopeBatch) {
@@ -429,7 +431,10 @@ int launch_rope_fast_inst(const RopeParams& p, cudaStream_t stream) {
   const int64_t blocks = (warps + kRopeWarps - 1) / kRopeWarps;
   B200_CHECK_ARG(blocks > 0 && blocks < (int64_t)0x7fffffff, "rope_store_kv: too many rows (%lld)",
                  (long long)p.num_tokens);
-  rope_store_fast_kernel<SRC, DST, D, NEOX><<<(unsigned)blocks, kRopeWarps * 32, 0, stream>>>(fp);
+  if (p.k_cache != nullptr && (p.k_scale != 1.0f || p.v_scale != 1.0f))
+    rope_store_fast_kernel<SRC, DST, D, NEOX, true><<<(unsigned)blocks, kRopeWarps * 32, 0, stream>>>(fp);
+  else
+    rope_store_fast_kernel<SRC, DST, D, NEOX, false><<<(unsigned)blocks, kRopeWarps * 32, 0, stream>>>(fp);
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;
 }
