@@ -218,6 +218,9 @@ def main():
         emit(extend_case("cfg5/16 with FP8-e4m3 KV pool", 8, 16384, 1024, 32, 8, 128, it, pool_dtype=e4))
         emit(extend_case("prefill 8 req x 4K no prefix", 8, 0, 4096, 32, 8, 128, it))
         emit(extend_case("70B tp8 4 req x (8K + 2K)", 4, 8192, 2048, 8, 1, 128, it))
+        emit(extend_case("D64 qwen2.5-0.5b heads 8 req x (16K shared prefix + 1K)", 8, 16384, 1024, 14, 2, 64, it))
+        emit(extend_case("D64 32/8 heads 8 req x (16K shared prefix + 1K)", 8, 16384, 1024, 32, 8, 64, it))
+        emit(extend_case("D64 32/8 heads, generic kernel (CUDA cores), 2 req", 2, 16384, 1024, 32, 8, 64, 3, kernel=1))
     if a.json:
         Path(a.json).write_text(json.dumps(out, indent=1))
 

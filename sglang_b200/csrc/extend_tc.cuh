@@ -36,7 +36,7 @@
 namespace {
 namespace tc {
 
-constexpr int kD = 128;            // head dim of this instance
+constexpr int kD = 128;            // head dim the tiles are laid out for (kHD = 64 uses the first 64-wide half)
 constexpr int kBlockKV = 128;      // kv tokens per MMA block
 constexpr int kQTiles = 2;
 constexpr int kSoftmaxWarps = 4;                     // per query tile
@@ -92,7 +92,11 @@ __device__ __forceinline__ uint32_t swz_off(int row, int chunk, int rows) {
 // kFp8: the pool holds FP8-e4m3 bytes; the MMAs then run in f16 (e4m3 -> f16 is exact) on tiles the producers
 // dequantise, Q is converted to f16 on its way into shared memory and P is packed as f16.
 // kOpts: sliding window / logit cap / attention sinks compiled in (the plain causal instance stays untouched).
-template <typename QT, int kEmu, bool kFp8, bool kOpts>
+// kHD: head dim, 128 or 64.  The 64 instance keeps the 128 instance's tile geometry and barrier protocol and simply
+// never touches the second 64-wide d half: the producers fill 128-byte rows, QK runs 4 k-steps instead of 8, PV is
+// an M128 x N64 MMA into 64 O columns.  (Its softmax cost per kv block is the same as for D = 128, so it is
+// exp-bound rather than MMA-bound.)
+template <typename QT, int kEmu, bool kFp8, bool kOpts, int kHD>
 __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const ExtendParams p, const int max_tiles) {
   using namespace tc;
   using namespace ptx;
@@ -178,7 +182,7 @@ __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const Extend
 }
 
 bool extend_fast_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype) {
-  if (dqk != tc::kD || dv != tc::kD) return false;
+  if (dqk != dv || (dqk != 128 && dqk != 64)) return false;
   if (group < 1 || group > 128) return false;
   if (q_dtype != B200_BF16 && q_dtype != B200_F16) return false;
   return kv_dtype == q_dtype || kv_dtype == B200_FP8_E4M3;
@@ -197,11 +201,11 @@ bool extend_fast_layout_ok(const ExtendParams& p, int kv_dtype) {
          p.k_stride_s > 0 && p.v_stride_s > 0 && p.k_stride_s < (1ll << 30) && p.v_stride_s < (1ll << 30);
 }
 
-template <typename QT, int kEmu, bool kFp8, bool kOpts>
+template <typename QT, int kEmu, bool kFp8, bool kOpts, int kHD>
 int launch_extend_fast_t(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   static bool configured = false;
   constexpr int kSmem = tc::Layout<kFp8>::kSmemBytes;
-  auto kern = extend_tc_kernel<QT, kEmu, kFp8, kOpts>;
+  auto kern = extend_tc_kernel<QT, kEmu, kFp8, kOpts, kHD>;
   if (!configured) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     configured = true;
@@ -228,14 +232,20 @@ int extend_emu_eighths() {
   return v;
 }
 
-template <typename QT, bool kFp8>
-int launch_extend_fast_q(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
+template <typename QT, bool kFp8, int kHD>
+int launch_extend_fast_d(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr;
   if (extend_emu_eighths() == 0)
-    return opts ? launch_extend_fast_t<QT, 0, kFp8, true>(p, a, stream)
-                : launch_extend_fast_t<QT, 0, kFp8, false>(p, a, stream);
-  return opts ? launch_extend_fast_t<QT, 3, kFp8, true>(p, a, stream)
-              : launch_extend_fast_t<QT, 3, kFp8, false>(p, a, stream);
+    return opts ? launch_extend_fast_t<QT, 0, kFp8, true, kHD>(p, a, stream)
+                : launch_extend_fast_t<QT, 0, kFp8, false, kHD>(p, a, stream);
+  return opts ? launch_extend_fast_t<QT, 3, kFp8, true, kHD>(p, a, stream)
+              : launch_extend_fast_t<QT, 3, kFp8, false, kHD>(p, a, stream);
+}
+
+template <typename QT, bool kFp8>
+int launch_extend_fast_q(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
+  return p.head_dim_qk == 64 ? launch_extend_fast_d<QT, kFp8, 64>(p, a, stream)
+                             : launch_extend_fast_d<QT, kFp8, 128>(p, a, stream);
 }
 
 int launch_extend_fast(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {

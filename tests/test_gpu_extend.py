@@ -77,7 +77,9 @@ SHAPES = [
     # Hq, Hkv, D, prefix, extend, page
     (32, 8, 128, [0, 130, 64], [257, 1, 128], 1),      # Llama-8B heads; no-prefix, single-token and exact tiles
     (8, 1, 128, [700], [300], 16),                     # 70B TP8 shard
-    (14, 2, 64, [512, 512], [63, 5], 1),               # Qwen2.5-0.5B heads
+    (14, 2, 64, [512, 512], [63, 5], 1),               # Qwen2.5-0.5B heads (group 7) -> kHD = 64 tcgen05 instance
+    (16, 4, 64, [300, 0, 127], [260, 129, 1], 16),     # D 64, group 4: several q tiles and kv blocks, page 16
+    (4, 4, 64, [200], [400], 1),                       # D 64 MHA: 128 tokens per q tile
     (4, 4, 80, [10, 0], [33, 17], 1),                  # odd head dim -> generic
     (4, 4, 256, [33], [70], 32),
     (16, 1, 128, [100], [150], 1),                     # group 16
@@ -96,6 +98,16 @@ def test_extend_vs_oracle(shape, dtype, pool_dtype, kernel):
     want = ref.extend_ref(q, kp, vp, rtt, rpi, pre, ext, scale, kv_dtype=pool_dtype)
     err = float((got - want).abs().max())
     assert err <= ATOL, f"max-abs {err}"
+
+
+def test_fast_path_covers_d64_and_d128():
+    from sglang_b200 import ops
+
+    for D in (64, 128):
+        for kv in (torch.bfloat16, torch.float8_e4m3fn):
+            assert ops.extend_fast_supported(D, D, 4, torch.bfloat16, kv)
+    assert not ops.extend_fast_supported(80, 80, 4, torch.bfloat16, torch.bfloat16)
+    assert not ops.extend_fast_supported(128, 64, 4, torch.bfloat16, torch.bfloat16)
 
 
 def test_extend_non_causal_and_lse():

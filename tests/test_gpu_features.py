@@ -131,7 +131,8 @@ EXT_SHAPES = [
     (32, 8, 128, [0, 700, 130], [300, 260, 1], 1),       # Llama-8B heads: several q tiles, windows crossing blocks
     (8, 1, 128, [1500], [600], 16),                      # group 8, long prefix: whole leading blocks are skipped
     (16, 16, 128, [5, 0], [250, 129], 1),                # MHA: 128 tokens per q tile
-    (4, 2, 64, [40, 0], [33, 70], 1),                    # generic path
+    (14, 2, 64, [600, 3], [200, 140], 1),                # D 64 (Qwen2.5-0.5B heads): the kHD = 64 instance with options
+    (4, 2, 64, [40, 0], [33, 70], 1),                    # D 64, group 2, short sequences
 ]
 
 
