@@ -96,7 +96,7 @@ def decode_case(name, bs, L, Hq, Hkv, D, pool_dtype, page, iters, ragged=False):
                 us_eager=round(t_eager * 1e6, 1))
 
 
-def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_dtype=torch.bfloat16):
+def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_dtype=torch.bfloat16, tree_mask=False):
     dev = "cuda"
     g = torch.Generator(device=dev).manual_seed(0)
     rows = (P if shared else bs * P) + bs * E + 1
@@ -122,8 +122,15 @@ def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_d
     ws = ops.ExtendWorkspace.create(bs, T // bq + bs + 1, dev, num_ctas=sm)
     ops.extend_plan(ws, ext, bq)
 
+    mkw = {}
+    if tree_mask:   # TARGET_VERIFY shape: a chain "tree" (lower-triangular) over the E draft tokens, prefix unmasked
+        m = torch.ones(bs, E, P + E, dtype=torch.uint8, device=dev)
+        m[:, :, P:] = torch.tril(torch.ones(E, E, dtype=torch.uint8, device=dev))
+        mkw = dict(custom_mask=m.reshape(-1), mask_skip_prefix=True,
+                   mask_indptr=torch.arange(bs + 1, device=dev, dtype=torch.int64) * (E * (P + E)))
+
     def fn():
-        ops.extend_attention(q, o, kp, vp, rtt, rpi, pre, ext, ws, D**-0.5, kernel=kernel, kv_dtype=pool_dtype)
+        ops.extend_attention(q, o, kp, vp, rtt, rpi, pre, ext, ws, D**-0.5, kernel=kernel, kv_dtype=pool_dtype, **mkw)
 
     t = time_cuda(fn, iters, warmup=2)
     flops = 4 * Hq * D * bs * (E * P + E * (E + 1) / 2)
@@ -218,6 +225,10 @@ def main():
         emit(extend_case("cfg5/16 with FP8-e4m3 KV pool", 8, 16384, 1024, 32, 8, 128, it, pool_dtype=e4))
         emit(extend_case("prefill 8 req x 4K no prefix", 8, 0, 4096, 32, 8, 128, it))
         emit(extend_case("70B tp8 4 req x (8K + 2K)", 4, 8192, 2048, 8, 1, 128, it))
+        emit(extend_case("verify 64 req x (4K + 8 draft, tree mask), tcgen05", 64, 4096, 8, 32, 8, 128, it,
+                         shared=False, tree_mask=True))
+        emit(extend_case("verify 64 req x (4K + 8 draft, tree mask), generic", 64, 4096, 8, 32, 8, 128, 3,
+                         shared=False, tree_mask=True, kernel=1))
         emit(extend_case("D64 qwen2.5-0.5b heads 8 req x (16K shared prefix + 1K)", 8, 16384, 1024, 14, 2, 64, it))
         emit(extend_case("D64 32/8 heads 8 req x (16K shared prefix + 1K)", 8, 16384, 1024, 32, 8, 64, it))
         emit(extend_case("D64 32/8 heads, generic kernel (CUDA cores), 2 req", 2, 16384, 1024, 32, 8, 64, 3, kernel=1))

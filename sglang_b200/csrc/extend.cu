@@ -273,9 +273,7 @@ extern "C" int b200attn_extend(const b200_extend_args* a, b200_stream_t stream_)
   B200_CHECK_ARG(!(a->kernel == B200_KERNEL_FAST && !fast_ok),
                  "extend: fast kernel does not cover Dk=%d Dv=%d group=%d q=%d kv=%d (or unaligned strides)",
                  a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype);
-  B200_CHECK_ARG(!(a->kernel == B200_KERNEL_FAST && a->custom_mask != nullptr),
-                 "extend: custom masks run on the generic kernel only");
-  const bool use_fast = fast_ok && a->kernel != B200_KERNEL_GENERIC && a->custom_mask == nullptr;
+  const bool use_fast = fast_ok && a->kernel != B200_KERNEL_GENERIC;
   if (use_fast) return launch_extend_fast(p, *a, stream);
   if (a->q_dtype == B200_BF16) return launch_generic<__nv_bfloat16>(p, a->kv_dtype, a->num_ctas, stream);
   return launch_generic<__half>(p, a->kv_dtype, a->num_ctas, stream);

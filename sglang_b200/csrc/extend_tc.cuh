@@ -91,7 +91,8 @@ __device__ __forceinline__ uint32_t swz_off(int row, int chunk, int rows) {
 // kEmu: how many of every 8 column pairs take the polynomial exp2 (FMA pipe) instead of MUFU.EX2.
 // kFp8: the pool holds FP8-e4m3 bytes; the MMAs then run in f16 (e4m3 -> f16 is exact) on tiles the producers
 // dequantise, Q is converted to f16 on its way into shared memory and P is packed as f16.
-// kOpts: sliding window / logit cap / attention sinks compiled in (the plain causal instance stays untouched).
+// kOpts: sliding window / logit cap / attention sinks / custom masks compiled in (the plain causal instance stays
+// untouched).
 // kHD: head dim, 128 or 64.  The 64 instance keeps the 128 instance's tile geometry and barrier protocol and simply
 // never touches the second 64-wide d half: the producers fill 128-byte rows, QK runs 4 k-steps instead of 8, PV is
 // an M128 x N64 MMA into 64 O columns.  (Its softmax cost per kv block is the same as for D = 128, so it is
@@ -127,7 +128,9 @@ __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const Extend
   const int64_t pool_row = load_index(p.req_pool_indices, p.req_pool_indices_is_i64, req);
   const int q_tok0 = qo_indptr[req] + q_start;            // first global q row of this item
   const int n_q = min(kQTiles * BQ, E - q_start);          // valid query tokens in this item
-  const int kv_end = p.causal ? P + q_start + n_q : P + E; // kv positions [kv_off, kv_end) are needed
+  // a custom (tree) mask replaces the causal rule on the new tokens: every row may see all P + E positions
+  const bool masked = kOpts && p.custom_mask != nullptr;
+  const int kv_end = (p.causal && !masked) ? P + q_start + n_q : P + E;   // kv positions [kv_off, kv_end) are needed
   // sliding window: the first query of the item sees nothing before P + q_start + 1 - window_keys, so whole
   // 128-token blocks below that are skipped; all three roles count blocks from kv_off
   const int kv_first =
@@ -234,7 +237,7 @@ int extend_emu_eighths() {
 
 template <typename QT, bool kFp8, int kHD>
 int launch_extend_fast_d(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
-  const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr;
+  const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr || p.custom_mask != nullptr;
   if (extend_emu_eighths() == 0)
     return opts ? launch_extend_fast_t<QT, 0, kFp8, true, kHD>(p, a, stream)
                 : launch_extend_fast_t<QT, 0, kFp8, false, kHD>(p, a, stream);

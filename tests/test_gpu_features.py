@@ -156,12 +156,13 @@ def test_extend_options(shape, opts, pool_dtype):
         assert float((lse - want_lse).abs().max()) <= ATOL, f"kernel {kernel} lse"
 
 
-def test_extend_custom_mask_large():
-    """Tree mask over 64 draft tokens on top of a 900-token prefix, D 128 (generic kernel: custom masks are not on
-    the tensor path), both SKIP_PREFIX_CUSTOM_MASK settings."""
-    Hq, Hkv, D = 8, 2, 128
-    prefix, extend = [900, 17], [64, 64]
-    q, kp, vp, rtt, rpi, pre, ext = make_extend_problem(Hq, Hkv, D, prefix, extend, 1, torch.bfloat16, torch.bfloat16, 21)
+@pytest.mark.parametrize("pool_dtype", [torch.bfloat16, torch.float8_e4m3fn])
+@pytest.mark.parametrize("Hq,Hkv,D", [(8, 2, 128), (14, 2, 64), (4, 4, 80)])
+def test_extend_custom_mask_large(Hq, Hkv, D, pool_dtype):
+    """Tree mask over 64 draft tokens on top of a 900-token prefix, both SKIP_PREFIX_CUSTOM_MASK settings, with and
+    without a sliding window; D 128 / 64 run the tcgen05 kernel (kOpts instance) and the generic one, D 80 generic."""
+    prefix, extend = [900, 17, 0], [64, 64, 150]
+    q, kp, vp, rtt, rpi, pre, ext = make_extend_problem(Hq, Hkv, D, prefix, extend, 1, torch.bfloat16, pool_dtype, 21)
     g = torch.Generator().manual_seed(4)
     parts, offs = [], [0]
     for P, E in zip(prefix, extend):
@@ -172,10 +173,15 @@ def test_extend_custom_mask_large():
         offs.append(offs[-1] + E * (P + E))
     mask, indptr = torch.cat(parts).to(torch.uint8), torch.tensor(offs, dtype=torch.int64)
     for skip in (True, False):
-        kw = dict(custom_mask=mask, mask_indptr=indptr, mask_skip_prefix=skip)
-        got, _ = _extend(q, kp, vp, rtt, rpi, pre, ext, D ** -0.5, torch.bfloat16, **kw)
-        want = ref.extend_ref(q, kp, vp, rtt, rpi, pre, ext, D ** -0.5, **kw)
-        assert float((got - want).abs().max()) <= ATOL, f"skip_prefix={skip}"
+        for window in (0, 200):
+            kw = dict(custom_mask=mask, mask_indptr=indptr, mask_skip_prefix=skip, window_keys=window)
+            want, want_lse = ref.extend_ref(q, kp, vp, rtt, rpi, pre, ext, D ** -0.5, kv_dtype=pool_dtype,
+                                            want_lse=True, **kw)
+            for kernel in (0, 1):
+                got, lse = _extend(q, kp, vp, rtt, rpi, pre, ext, D ** -0.5, pool_dtype, kernel=kernel,
+                                   want_lse=True, **kw)
+                assert float((got - want).abs().max()) <= ATOL, f"skip_prefix={skip} window={window} kernel={kernel}"
+                assert float((lse - want_lse).abs().max()) <= ATOL, f"lse skip_prefix={skip} kernel={kernel}"
 
 
 # ----------------------------------------------------------------------------- merge_state
