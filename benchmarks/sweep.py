@@ -102,7 +102,7 @@ def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_d
     rows = (P if shared else bs * P) + bs * E + 1
     kp = torch.randn(rows, Hkv, D, generator=g, device=dev, dtype=torch.bfloat16)
     vp = torch.randn(rows, Hkv, D, generator=g, device=dev, dtype=torch.bfloat16)
-    if pool_dtype == torch.float8_e4m3fn:
+    if pool_dtype in (torch.float8_e4m3fn, torch.float8_e5m2):
         kp, vp = kp.to(pool_dtype).view(torch.uint8), vp.to(pool_dtype).view(torch.uint8)
     perm = torch.randperm(rows - 1, generator=g, device=dev).int() + 1
     rtt = torch.zeros(bs + 1, P + E, dtype=torch.int32, device=dev)
@@ -223,6 +223,7 @@ def main():
             emit(extend_case("cfg5 128 req x (16K shared prefix + 1K)", 128, 16384, 1024, 32, 8, 128, it))
             emit(extend_case("cfg5 no sharing 16 req x (16K + 1K)", 16, 16384, 1024, 32, 8, 128, it, shared=False))
         emit(extend_case("cfg5/16 with FP8-e4m3 KV pool", 8, 16384, 1024, 32, 8, 128, it, pool_dtype=e4))
+        emit(extend_case("cfg5/16 with FP8-e5m2 KV pool", 8, 16384, 1024, 32, 8, 128, it, pool_dtype=torch.float8_e5m2))
         emit(extend_case("prefill 8 req x 4K no prefix", 8, 0, 4096, 32, 8, 128, it))
         emit(extend_case("70B tp8 4 req x (8K + 2K)", 4, 8192, 2048, 8, 1, 128, it))
         emit(extend_case("verify 64 req x (4K + 8 draft, tree mask), tcgen05", 64, 4096, 8, 32, 8, 128, it,

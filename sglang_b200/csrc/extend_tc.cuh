@@ -89,7 +89,7 @@ __device__ __forceinline__ uint32_t swz_off(int row, int chunk, int rows) {
 }  // namespace tc
 
 // kEmu: how many of every 8 column pairs take the polynomial exp2 (FMA pipe) instead of MUFU.EX2.
-// kFp8: the pool holds FP8-e4m3 bytes; the MMAs then run in f16 (e4m3 -> f16 is exact) on tiles the producers
+// kFp8: the pool holds FP8 bytes (e4m3, or e5m2 when p.kv_e5m2); the MMAs then run in f16 (both widenings are exact) on tiles the producers
 // dequantise, Q is converted to f16 on its way into shared memory and P is packed as f16.
 // kOpts: sliding window / logit cap / attention sinks / custom masks compiled in (the plain causal instance stays
 // untouched).
@@ -188,14 +188,14 @@ bool extend_fast_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype
   if (dqk != dv || (dqk != 128 && dqk != 64)) return false;
   if (group < 1 || group > 128) return false;
   if (q_dtype != B200_BF16 && q_dtype != B200_F16) return false;
-  return kv_dtype == q_dtype || kv_dtype == B200_FP8_E4M3;
+  return kv_dtype == q_dtype || kv_dtype == B200_FP8_E4M3 || kv_dtype == B200_FP8_E5M2;
 }
 
 // query tokens per work item (two 128-row tiles of 128/group tokens each)
 int extend_fast_block_q(int group) { return tc::kQTiles * (128 / group); }
 
 bool extend_fast_layout_ok(const ExtendParams& p, int kv_dtype) {
-  const int kv_align = kv_dtype == B200_FP8_E4M3 ? 16 : 8;     // pool rows are read in 16-byte pieces
+  const int kv_align = (kv_dtype == B200_FP8_E4M3 || kv_dtype == B200_FP8_E5M2) ? 16 : 8;   // 16-byte pieces
   auto a16 = [](const void* ptr) { return ((uintptr_t)ptr & 15) == 0; };
   return a16(p.k_cache) && a16(p.v_cache) && a16(p.q) && a16(p.o) && p.k_stride_s % kv_align == 0 &&
          p.k_stride_h % kv_align == 0 && p.v_stride_s % kv_align == 0 && p.v_stride_h % kv_align == 0 &&
@@ -252,7 +252,7 @@ int launch_extend_fast_q(const ExtendParams& p, const b200_extend_args& a, cudaS
 }
 
 int launch_extend_fast(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
-  const bool fp8 = a.kv_dtype == B200_FP8_E4M3;
+  const bool fp8 = a.kv_dtype == B200_FP8_E4M3 || a.kv_dtype == B200_FP8_E5M2;
   if (a.q_dtype == B200_BF16)
     return fp8 ? launch_extend_fast_q<__nv_bfloat16, true>(p, a, stream)
                : launch_extend_fast_q<__nv_bfloat16, false>(p, a, stream);

@@ -55,14 +55,14 @@ def test_pure_host_queries_work_without_gpu():
     assert ops.decode_fast_supported(128, 128, 8, torch.bfloat16, torch.float8_e4m3fn)
     assert not ops.decode_fast_supported(80, 80, 1, torch.bfloat16, torch.bfloat16)
     assert not ops.decode_fast_supported(128, 128, 32, torch.bfloat16, torch.bfloat16)
-    # tcgen05 extend instances: D 128 and D 64, bf16 / f16 / FP8-e4m3 pools; everything else is the generic kernel
+    # tcgen05 extend instances: D 128 and D 64, bf16 / f16 / FP8 (e4m3, e5m2) pools; everything else is the generic kernel
     for D in (64, 128):
         assert ops.extend_fast_supported(D, D, 4, torch.bfloat16, torch.bfloat16)
         assert ops.extend_fast_supported(D, D, 7, torch.float16, torch.float8_e4m3fn)
         assert ops.extend_block_q(D, D, 4, torch.bfloat16, torch.bfloat16) == 64   # 2 tiles x 128 / group tokens
     assert not ops.extend_fast_supported(256, 256, 4, torch.bfloat16, torch.bfloat16)
     assert not ops.extend_fast_supported(128, 64, 4, torch.bfloat16, torch.bfloat16)
-    assert not ops.extend_fast_supported(64, 64, 4, torch.bfloat16, torch.float8_e5m2)
+    assert ops.extend_fast_supported(128, 128, 4, torch.bfloat16, torch.float8_e5m2)
 
 
 def test_ops_refuse_cpu_tensors():

@@ -88,7 +88,7 @@ SHAPES = [
 
 @pytest.mark.parametrize("kernel", list(KERNELS))
 @pytest.mark.parametrize("dtype,pool_dtype", [(torch.bfloat16, torch.bfloat16), (torch.float16, torch.float16),
-                                              (torch.bfloat16, torch.float8_e4m3fn)])
+                                              (torch.bfloat16, torch.float8_e4m3fn), (torch.float16, torch.float8_e5m2)])
 @pytest.mark.parametrize("shape", SHAPES, ids=[f"h{s[0]}_{s[1]}_d{s[2]}_p{s[5]}" for s in SHAPES])
 def test_extend_vs_oracle(shape, dtype, pool_dtype, kernel):
     Hq, Hkv, D, prefix, extend, page = shape
