@@ -487,8 +487,18 @@ def run_ours(args):
     return 0
 
 
+def _reserve_stdout_for_the_json_line():
+    """Libraries write to fd 1 behind Python's back (NCCL prints "NCCL version ..." there under torchrun): point fd 1 at
+    stderr and keep the real stdout for this script's own print() — the one JSON line."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
+
+
 def main():
     args = parse_args()
+    _reserve_stdout_for_the_json_line()
     if args.impl == "reference":
         return run_reference(args)
     return run_ours(args)
