@@ -37,7 +37,7 @@ def _lib() -> C.CDLL:
     if _LIB is None:
         path = Path(__file__).resolve().parent / "_build" / "liboracle_kv.so"
         if not path.exists():
-            from sglang_b200.build import build_oracle
+            from oracle.build_oracle import build_oracle
 
             build_oracle()
         lib = C.CDLL(str(path))

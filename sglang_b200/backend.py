@@ -36,6 +36,43 @@ def _attn_tp_size(model_runner) -> int:
         return int(getattr(model_runner, "attn_tp_size", 1) or 1)
 
 
+def _spec_num_draft_tokens(model_runner) -> int:
+    """`--speculative-num-draft-tokens` (triton_backend.py:171), 0 without speculative decoding."""
+    try:
+        from sglang.srt.runtime_context import get_spec  # type: ignore
+
+        n = get_spec().speculative_num_draft_tokens
+    except Exception:
+        n = getattr(getattr(model_runner, "server_args", None), "speculative_num_draft_tokens", None)
+    return int(n or 0)
+
+
+class _ExtendState:
+    """One set of extend-side device buffers: planner work list, per-request length vectors for the
+    speculative modes (int32 and int64 flavours, matching `seq_lens`), custom-mask bytes and their indptr."""
+
+    def __init__(self, ws, max_bs, mask, device):
+        self.ws, self.max_bs, self.max_tiles, self.mask = ws, max_bs, ws.max_tiles, mask
+        self._ext = {dt: torch.zeros(max_bs, dtype=dt, device=device) for dt in (torch.int32, torch.int64)}
+        self._pre = {dt: torch.zeros(max_bs, dtype=dt, device=device) for dt in (torch.int32, torch.int64)}
+        self.mask_indptr = torch.zeros(max_bs + 1, dtype=torch.int64, device=device)
+
+    @staticmethod
+    def create(max_bs, max_tiles, mask_bytes, device, num_ctas) -> "_ExtendState":
+        ws = ops.ExtendWorkspace.create(max_bs, max_tiles, device, num_ctas=num_ctas)
+        mask = torch.zeros(max(int(mask_bytes), 1), dtype=torch.uint8, device=device)
+        return _ExtendState(ws, max_bs, mask, device)
+
+    def fits(self, bs, tiles, mask_bytes) -> bool:
+        return bs <= self.max_bs and tiles <= self.max_tiles and mask_bytes <= self.mask.numel()
+
+    def ext_lens(self, dtype):
+        return self._ext[dtype]
+
+    def pre_lens(self, dtype):
+        return self._pre[dtype]
+
+
 class B200AttnBackend(_Base):
     #: rows of the fast decode kernel's work list per persistent CTA
     DECODE_WAVES = 16
@@ -90,10 +127,20 @@ class B200AttnBackend(_Base):
             self.max_bs, self.num_head, self.v_head_dim, dev, num_ctas=self.decode_ctas, waves=self.DECODE_WAVES)
         # second split-KV plan for the sliding-window layers (same partial buffers: layers run one after another)
         self.decode_ws_swa = self._swa_workspace(self.decode_ws)
-        self._verify_ext: Optional[torch.Tensor] = None
-        self._mask_indptr: Optional[torch.Tensor] = None
-        self.extend_ws: Optional[ops.ExtendWorkspace] = None
-        self._extend_block_q = 64
+        # Extend-side state comes in two sets (see _ExtendState): `_ext_graph` is allocated once by
+        # init_cuda_graph_state and never touched again (its addresses are baked into captured graphs);
+        # `_ext_eager` grows on demand for eager batches that do not fit it.  `_ext` is the set the current
+        # forward uses, chosen in init_forward_metadata_out_graph.
+        self._ext_graph: Optional[_ExtendState] = None
+        self._ext_eager: Optional[_ExtendState] = None
+        self._ext: Optional[_ExtendState] = None
+        self._ext_captured = {}        # (mode, padded bs) -> the set a captured graph holds
+        self._ext_lens = None          # (prefix_lens, extend_lens, custom_mask, mask_indptr) of this forward
+        self._graph_state_frozen = False
+        group = self.num_head // self.num_kv_head
+        self._extend_block_q = ops.extend_block_q(self.head_dim, self.v_head_dim, group, self._q_dtype,
+                                                  self.kv_dtype, self.extend_kernel)
+        self.num_draft_tokens = _spec_num_draft_tokens(model_runner)
         self.forward_metadata = None
         #: optional (start, stop) torch.cuda.Event pair re-recorded around the next decode attention kernel
         self.attn_events = None
@@ -117,41 +164,121 @@ class B200AttnBackend(_Base):
         return int(n)
 
     # ------------------------------------------------------------------ metadata
-    def init_forward_metadata_out_graph(self, forward_batch, in_capture: bool = False):
-        """Host-side prep only: (re)size the extend work list from host-known counts.
+    @property
+    def extend_ws(self):
+        return self._ext.ws if self._ext is not None else None
 
-        Decode needs nothing here: the planner kernel reads `seq_lens` on the device, so a
-        graph replay only has to refresh the runner's static `seq_lens`/`req_pool_indices`."""
+    def _select_ext(self, key, bs: int, tokens: int, mask_bytes: int, in_capture: bool) -> "_ExtendState":
+        """Pick the extend-side buffer set for this forward.
+
+        A capture records which set it baked into the graph under `key` = (mode, padded batch size); every later
+        call with that key (the replays, and eager batches of the same shape -- a forward never interleaves with
+        a replay) gets the same set back, so the replay refills exactly the buffers the graph reads.  Sets that a
+        graph holds are never reallocated or freed; other eager batches use the graph set when they
+        fit it, else a separate eager set that grows geometrically."""
+        tiles = tokens // self._extend_block_q + bs + 1
+        st = self._ext_captured.get(key)
+        if st is not None and st.fits(bs, tiles, mask_bytes):
+            return st
+        g = self._ext_graph
+        if in_capture:
+            if g is None or not g.fits(bs, tiles, mask_bytes):
+                # init_cuda_graph_state under-sized it (e.g. no speculative config on the runner): allocate a
+                # bigger set for this and later captures; older graphs keep theirs alive through _ext_captured
+                dims = (g.max_bs, g.max_tiles, g.mask.numel()) if g else (0, 0, 0)
+                g = _ExtendState.create(max(bs, dims[0]), max(tiles, dims[1]), max(mask_bytes, dims[2]),
+                                        self.device, self.sm_count)
+                self._ext_graph = g
+            self._ext_captured[key] = g
+            return g
+        if g is not None and g.fits(bs, tiles, mask_bytes):
+            return g
+        e = self._ext_eager
+        if e is None or not e.fits(bs, tiles, mask_bytes):
+            old_bs, old_tiles, old_mask = (e.max_bs, e.max_tiles, e.mask.numel()) if e else (0, 0, 0)
+            e = _ExtendState.create(
+                max(self.max_bs, bs, old_bs),
+                tiles if tiles <= old_tiles else max(tiles, 2 * old_tiles),
+                mask_bytes if mask_bytes <= old_mask else max(mask_bytes, 2 * old_mask),
+                self.device, self.sm_count)
+            self._ext_eager = e
+        return e
+
+    def _spec_tokens_per_req(self, forward_batch) -> int:
+        """Fixed query rows per request of the speculative graph modes (triton_backend.py:470-475,538-546)."""
+        mode, spec = forward_batch.forward_mode, getattr(forward_batch, "spec_info", None)
+        if mode.is_target_verify():
+            return self._draft_token_num(forward_batch)
+        n = getattr(spec, "num_tokens_per_req", None)
+        if n is None or int(n) <= 0:
+            n = self.num_draft_tokens
+        if int(n) <= 0:
+            raise ValueError("draft-extend under CUDA graphs needs spec_info.num_tokens_per_req or "
+                             "server_args.speculative_num_draft_tokens")
+        return int(n)
+
+    def init_forward_metadata_out_graph(self, forward_batch, in_capture: bool = False):
+        """Per-forward host-side prep, outside graph capture (base_attn_backend.py:59-79).
+
+        Decode needs nothing: the planner kernel reads `seq_lens` on the device, so a replay only has to refresh
+        the runner's static `seq_lens` / `req_pool_indices`.  Extend modes choose the buffer set and fill the
+        per-request length / mask buffers the recorded launches read (the reference's Triton backend does the
+        same refill in `_apply_cuda_graph_metadata`, triton_backend.py:572-634)."""
         mode = forward_batch.forward_mode
+        if in_capture:
+            self._graph_state_frozen = True
         if mode.is_decode_or_idle():
-            if forward_batch.batch_size > self.max_bs:
-                raise ValueError(f"batch size {forward_batch.batch_size} exceeds pool size {self.max_bs}")
+            if forward_batch.batch_size > self.decode_ws.max_bs:
+                raise ValueError(f"batch size {forward_batch.batch_size} exceeds the decode workspace "
+                                 f"({self.decode_ws.max_bs} requests)")
             return
         bs = int(forward_batch.batch_size)
+        spec = getattr(forward_batch, "spec_info", None)
+        eager_lens = getattr(forward_batch, "extend_prefix_lens", None) is not None and not in_capture
         if mode.is_target_verify():
-            # every request extends by draft_token_num tokens over a prefix of seq_lens tokens
-            # (triton_backend.py:807-866); the per-request lengths live in static buffers
-            T = bs * self._draft_token_num(forward_batch)
-            if self._verify_ext is None or self._verify_ext.shape[0] < bs:
-                n = max(self.max_bs, bs)
-                self._verify_ext = torch.zeros(n, dtype=forward_batch.seq_lens.dtype, device=self.device)
-                self._mask_indptr = torch.zeros(n + 1, dtype=torch.int64, device=self.device)
+            # every request extends by draft_token_num tokens over `seq_lens` cached ones (triton_backend.py:807-866)
+            n = self._spec_tokens_per_req(forward_batch)
+            mask = getattr(spec, "custom_mask", None)
+            st = self._select_ext((int(mode), bs), bs, bs * n, 0 if mask is None else int(mask.numel()), in_capture)
+            pre = forward_batch.seq_lens[:bs]
+            ext = st.ext_lens(pre.dtype)[:bs]
+            ext.fill_(n)
+            mask_indptr = None
+            if mask is not None:
+                # the mask tensor of a replay is not the capture-time one: copy it into the persistent buffer
+                # (triton_backend.py:507-514)
+                m = mask.view(torch.uint8) if mask.dtype == torch.bool else mask
+                st.mask[: m.numel()].copy_(m, non_blocking=True)
+                mask_indptr = st.mask_indptr[: bs + 1]
+                torch.cumsum((pre.to(torch.int64) + n) * n, dim=0, out=mask_indptr[1:])
+                mask = st.mask
+            self._ext, self._ext_lens = st, (pre, ext, mask, mask_indptr)
+        elif not eager_lens and mode.is_draft_extend_v2():
+            # CUDA-graph draft-extend: a fixed number of query rows per request; the cached prefix is
+            # seq_lens - accepted tokens, clamped for padded rows (triton_backend.py:529-565)
+            n = self._spec_tokens_per_req(forward_batch)
+            st = self._select_ext((int(mode), bs), bs, bs * n, 0, in_capture)
+            seq = forward_batch.seq_lens[:bs]
+            ext = st.ext_lens(seq.dtype)[:bs]
+            ext.fill_(n)
+            pre = st.pre_lens(seq.dtype)[:bs]
+            acc = getattr(spec, "extend_seq_lens_tensor", None)
+            if acc is None:
+                acc = getattr(spec, "num_accept_tokens", None)
+            if acc is not None:
+                torch.clamp(seq - acc[:bs].to(seq.dtype), min=0, out=pre)
+            else:
+                pre.copy_(seq)
+            self._ext, self._ext_lens = st, (pre, ext, None, None)
         else:
-            T = int(forward_batch.extend_num_tokens if forward_batch.extend_num_tokens is not None
-                    else forward_batch.out_cache_loc.shape[0])
-        group = self.num_head // self.num_kv_head
-        q_dtype = self._q_dtype_hint
-        self._extend_block_q = ops.extend_block_q(self.head_dim, self.v_head_dim, group, q_dtype,
-                                                  self.kv_dtype, self.extend_kernel)
-        need_tiles = T // self._extend_block_q + bs + 1
-        ws = self.extend_ws
-        if ws is None or ws.max_tiles < need_tiles or ws.max_bs < bs:
-            self.extend_ws = ops.ExtendWorkspace.create(
-                max(self.max_bs, bs), max(need_tiles, 2 * (ws.max_tiles if ws else 0)), self.device,
-                num_ctas=self.sm_count)
+            T = getattr(forward_batch, "extend_num_tokens", None)
+            if T is None:
+                T = forward_batch.out_cache_loc.shape[0]
+            self._ext = self._select_ext((int(mode), bs), bs, int(T), 0, in_capture)
+            self._ext_lens = (forward_batch.extend_prefix_lens, forward_batch.extend_seq_lens, None, None)
 
     def init_forward_metadata_in_graph(self, forward_batch):
-        """One planner launch (static shape, graph-recordable, no host sync)."""
+        """One planner launch (static shape, graph-recordable, no host sync, reads persistent buffers only)."""
         mode = forward_batch.forward_mode
         if mode.is_idle():
             return
@@ -162,31 +289,31 @@ class B200AttnBackend(_Base):
             if self.decode_ws_swa is not None:
                 ops.decode_plan(self.decode_ws_swa, seq_lens, self.num_kv_head, waves=self.DECODE_WAVES,
                                 items_per_chunk=self._decode_items, window_keys=self.sliding_window_size + 1)
-        elif mode.is_target_verify():
-            bs, n = forward_batch.batch_size, self._draft_token_num(forward_batch)
-            ext = self._verify_ext[:bs]
-            ext.fill_(n)
-            pre = forward_batch.seq_lens[:bs]
-            torch.cumsum((pre.to(torch.int64) + n) * n, dim=0, out=self._mask_indptr[1 : bs + 1])
-            ops.extend_plan(self.extend_ws, ext, self._extend_block_q)
         else:
-            ops.extend_plan(self.extend_ws, forward_batch.extend_seq_lens, self._extend_block_q)
-
-    # model dtype is not on the runner contract; bf16 unless the runner says otherwise
-    @property
-    def _q_dtype_hint(self) -> torch.dtype:
-        return getattr(self, "_q_dtype", torch.bfloat16)
+            ops.extend_plan(self._ext.ws, self._ext_lens[1], self._extend_block_q)
 
     # ------------------------------------------------------------------ CUDA graphs
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
+        """Allocate every buffer whose address a captured graph will hold (decode_cuda_graph_runner.py:318,444
+        call this with the largest capture batch, usually far below the pool size).  Workspaces only ever GROW
+        here, and nothing is reallocated once a capture has started."""
+        max_bs, max_num_tokens = int(max_bs), int(max_num_tokens)
         if max_bs > self.decode_ws.max_bs:
+            if self._graph_state_frozen:
+                raise RuntimeError("b200 backend: init_cuda_graph_state asked for a larger batch after a graph "
+                                   "was captured; captured graphs hold the current workspace addresses")
             self.max_bs = max_bs
-            self._decode_items = ops.decode_items_per_chunk(self.num_head, self.num_kv_head, self.head_dim,
-                                                        self.v_head_dim, self._q_dtype, self.kv_dtype)
-        self.decode_ws = ops.DecodeWorkspace.create(
+            self.decode_ws = ops.DecodeWorkspace.create(
                 max_bs, self.num_head, self.v_head_dim, self.device, num_ctas=self.decode_ctas,
                 waves=self.DECODE_WAVES)
-        self.decode_ws_swa = self._swa_workspace(self.decode_ws)
+            self.decode_ws_swa = self._swa_workspace(self.decode_ws)
+        g = self._ext_graph
+        tiles = max_num_tokens // self._extend_block_q + max_bs + 1
+        # custom (tree) masks of TARGET_VERIFY: draft tokens x (context + draft tokens) bytes per request, the
+        # reference's bound (triton_backend.py:1013-1017)
+        mask_bytes = max_num_tokens * self.max_context_len if self.num_draft_tokens > 0 else 0
+        if g is None or not g.fits(max_bs, tiles, mask_bytes):
+            self._ext_graph = _ExtendState.create(max_bs, tiles, mask_bytes, self.device, self.sm_count)
 
     def get_cuda_graph_seq_len_fill_value(self):
         return 1
@@ -293,14 +420,9 @@ class B200AttnBackend(_Base):
         attn_type = getattr(layer, "attn_type", None)
         causal = not (getattr(attn_type, "value", attn_type) == _AT.ENCODER_ONLY.value)
         T = q.shape[0]
-        prefix_lens, extend_lens = forward_batch.extend_prefix_lens, forward_batch.extend_seq_lens
-        custom_mask = mask_indptr = None
-        if forward_batch.forward_mode.is_target_verify():
-            bs = forward_batch.batch_size
-            prefix_lens, extend_lens = forward_batch.seq_lens[:bs], self._verify_ext[:bs]
-            custom_mask = getattr(forward_batch.spec_info, "custom_mask", None)
-            if custom_mask is not None:
-                mask_indptr = self._mask_indptr[: bs + 1]
+        # chosen by init_forward_metadata_out_graph: persistent buffers under CUDA graphs
+        prefix_lens, extend_lens, custom_mask, mask_indptr = self._ext_lens
+        bs = extend_lens.shape[0]
         lse = None
         if getattr(forward_batch, "mha_return_lse", False):
             lse = torch.empty((T, layer.tp_q_head_num), dtype=torch.float32, device=q.device)
@@ -309,8 +431,8 @@ class B200AttnBackend(_Base):
             o.view(T, layer.tp_q_head_num, layer.v_head_dim),
             k_buf, v_buf,
             self.req_to_token_pool.req_to_token,
-            forward_batch.req_pool_indices, prefix_lens, extend_lens,
-            self.extend_ws, layer.scaling,
+            forward_batch.req_pool_indices[:bs], prefix_lens, extend_lens,
+            self._ext.ws, layer.scaling,
             kv_dtype=self.kv_dtype, k_scale=k_descale, v_scale=v_descale,
             logit_cap=self._logit_cap(layer), causal=causal,
             kernel=self.extend_kernel, lse=lse,

@@ -1,4 +1,4 @@
-"""In-tree nvcc build of libb200attn.so (sm_100a only) and of the CPU oracle helpers.
+"""In-tree nvcc build of libb200attn.so (sm_100a only).
 
     python -m sglang_b200.build            # build if sources are newer than the .so
     python -m sglang_b200.build --force
@@ -70,24 +70,11 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path:
     return LIB_PATH
 
 
-def build_oracle(force: bool = False) -> Path:
-    """gcc build of the C restatement of the KV-store byte work (oracle/, test infrastructure)."""
-    src = REPO_DIR / "oracle" / "kv_store_ref.c"
-    out_dir = REPO_DIR / "oracle" / "_build"
-    out = out_dir / "liboracle_kv.so"
-    if not force and not _stale(out, [src]):
-        return out
-    out_dir.mkdir(parents=True, exist_ok=True)
-    subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-o", str(out), str(src)], check=True)
-    return out
-
-
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     args = ap.parse_args(argv)
     build_cuda(force=args.force, verbose=True)
-    build_oracle(force=args.force)
     return 0
 
 

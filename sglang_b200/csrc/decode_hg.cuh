@@ -344,12 +344,9 @@ bool decode_hg_supported(const DecodeParams& p, int q_dtype, int kv_dtype) {
 template <int D, int KV, typename QT, bool UPPER>
 int launch_decode_hg_inst(const DecodeParams& p, int num_ctas, cudaStream_t stream) {
   using C = HgCfg<D, KV>;
-  static bool configured = false;
+  static std::atomic<uint64_t> configured{0};
   auto kern = decode_hg_kernel<D, KV, QT, UPPER>;
-  if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kCtaSmem));
-    configured = true;
-  }
+  B200_CHECK_CUDA(set_max_dynamic_smem(kern, C::kCtaSmem, configured));
   kern<<<num_ctas, kHG * kWarp, C::kCtaSmem, stream>>>(p);
   B200_CHECK_CUDA(cudaGetLastError());
   decode_merge_fast_kernel<QT, D><<<p.batch_size * p.num_q_heads, kFastWarps * kWarp, 0, stream>>>(p);

@@ -93,7 +93,13 @@ __global__ void __launch_bounds__(kFastWarps* kWarp) decode_merge_fast_kernel(co
   const int Hq = p.num_q_heads;
   const int req = blockIdx.x / Hq, h = blockIdx.x - req * Hq;
   const int c0 = p.plan[kPlanHeader + req], n = p.plan[kPlanHeader + req + 1] - c0;
-  if (n <= 1) return;   // single-chunk requests were written by the attention kernel
+  if (n == 1) return;   // single-chunk requests were written by the attention kernel
+  if (n <= 0) {         // a request with no attended token: zeros and lse = -inf, like decode_merge_kernel
+    QT* orow = reinterpret_cast<QT*>(p.o) + (int64_t)req * p.o_stride_t + (int64_t)h * p.o_stride_h;
+    for (int d = threadIdx.x; d < D; d += kFastWarps * kWarp) orow[d] = from_float<QT>(0.f);
+    if (p.lse != nullptr && threadIdx.x == 0) p.lse[(int64_t)req * Hq + h] = -INFINITY;
+    return;
+  }
   const float* lse = p.ws_lse + (int64_t)c0 * Hq + h;
   const float* po = p.ws_o + ((int64_t)c0 * Hq + h) * D + lane * kVec;
   float m = -INFINITY;
@@ -465,12 +471,9 @@ bool decode_fast_layout_ok(const DecodeParams& p, int kv_dtype) {
 template <int D, int KV, typename QT, bool UPPER>
 int launch_decode_fast_inst(const DecodeParams& p, int num_ctas, cudaStream_t stream) {
   using C = FastCfg<D, KV>;
-  static bool configured = false;
+  static std::atomic<uint64_t> configured{0};
   auto kern = decode_mma_kernel<D, KV, QT, UPPER>;
-  if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kCtaSmem));
-    configured = true;
-  }
+  B200_CHECK_CUDA(set_max_dynamic_smem(kern, C::kCtaSmem, configured));
   kern<<<num_ctas, kFastWarps * kWarp, C::kCtaSmem, stream>>>(p);
   B200_CHECK_CUDA(cudaGetLastError());
   decode_merge_fast_kernel<QT, D><<<p.batch_size * p.num_q_heads, kFastWarps * kWarp, 0, stream>>>(p);

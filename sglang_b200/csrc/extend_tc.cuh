@@ -206,13 +206,10 @@ bool extend_fast_layout_ok(const ExtendParams& p, int kv_dtype) {
 
 template <typename QT, int kEmu, bool kFp8, bool kOpts, int kHD>
 int launch_extend_fast_t(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
-  static bool configured = false;
+  static std::atomic<uint64_t> configured{0};
   constexpr int kSmem = tc::Layout<kFp8>::kSmemBytes;
   auto kern = extend_tc_kernel<QT, kEmu, kFp8, kOpts, kHD>;
-  if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-    configured = true;
-  }
+  B200_CHECK_CUDA(set_max_dynamic_smem(kern, kSmem, configured));
   const int block_q = extend_fast_block_q(p.group);
   // host-side bound on the number of work items: sum_r ceil(E_r / block_q) <= T / block_q + bs
   int64_t tiles = a.num_q_tokens / block_q + a.batch_size;

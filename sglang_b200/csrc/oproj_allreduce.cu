@@ -86,11 +86,14 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-// bounded spin on a flag written by a peer GPU
+// Bounded spin on a flag written by a peer GPU.  Flags are launch epochs and only ever grow, so the wait is
+// "at least `want`" (wrap-safe): a fast peer may already have posted epoch want + 1 for the same tile before this
+// rank polled -- its epoch-`want` data is then complete and still intact, because the staging buffers alternate
+// with the epoch's parity.
 __device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t want, int tag) {
   long long t0 = 0;
   uint32_t polls = 0;
-  while (ld_acquire_sys(p) != want) {
+  while ((int32_t)(ld_acquire_sys(p) - want) < 0) {
     if ((++polls & 1023u) == 0) {
       const long long now = clock64();
       if (t0 == 0) t0 = now;
@@ -500,20 +503,14 @@ extern "C" int b200attn_oproj_allreduce(const b200_oproj_allreduce_args* a, b200
   const int grid = n_tiles < sm_count() ? n_tiles : sm_count();   // every CTA resident: peers wait on each other
   B200_CHECK_ARG(grid > 0, "oproj_allreduce: no SMs?");
   if (a->dtype == B200_BF16) {
-    static bool configured = false;
+    static std::atomic<uint64_t> configured{0};
     auto kern = oproj_allreduce_kernel<__nv_bfloat16>;
-    if (!configured) {
-      B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax));
-      configured = true;
-    }
+    B200_CHECK_CUDA(set_max_dynamic_smem(kern, kSmemMax, configured));
     kern<<<grid, kThreads, smem_bytes, stream>>>(p);
   } else {
-    static bool configured = false;
+    static std::atomic<uint64_t> configured{0};
     auto kern = oproj_allreduce_kernel<__half>;
-    if (!configured) {
-      B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax));
-      configured = true;
-    }
+    B200_CHECK_CUDA(set_max_dynamic_smem(kern, kSmemMax, configured));
     kern<<<grid, kThreads, smem_bytes, stream>>>(p);
   }
   B200_CHECK_CUDA(cudaGetLastError());

@@ -16,7 +16,8 @@ def pytest_configure(config):
 @pytest.fixture(scope="session", autouse=True)
 def _built_library():
     """Build libb200attn.so and the C oracle once per session (nvcc cross-compiles without a GPU)."""
-    from sglang_b200.build import build_cuda, build_oracle
+    from oracle.build_oracle import build_oracle
+    from sglang_b200.build import build_cuda
 
     build_cuda()
     build_oracle()
