@@ -67,6 +67,9 @@ def build(force: bool = False) -> Path:
         raise FileNotFoundError("/root/reference is absent and oracle/_ref was not staged")
     manifest = DST / "MANIFEST.json"
     if manifest.exists() and not force:
+        # the stubs are this repo's own files: keep the staged copy current
+        shutil.rmtree(DST / "stubs", ignore_errors=True)
+        shutil.copytree(REPO / "oracle" / "stubs", DST / "stubs", ignore=_ignore)
         return DST
     if DST.exists():
         shutil.rmtree(DST)
