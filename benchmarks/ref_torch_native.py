@@ -38,9 +38,6 @@ def main() -> int:
     if not (REF / "MANIFEST.json").exists():
         print(json.dumps({"unavailable": "oracle/_ref is not staged"}))
         return 0
-    if os.environ.get("CUDA_VISIBLE_DEVICES") == "":
-        del os.environ["CUDA_VISIBLE_DEVICES"]
-    os.environ["CUDA_VISIBLE_DEVICES_SAVED"] = os.environ.get("CUDA_VISIBLE_DEVICES", "")
     sys.path[:0] = [str(REF / "stubs"), str(REF / "python")]
     import torch
 

@@ -11,9 +11,10 @@ from .attention_registry import ATTENTION_BACKENDS, register_attention_backend
 from .base_attn_backend import AttentionBackend
 from .forward_batch_info import ForwardBatch, ForwardMode
 from .memory_pool import KVWriteLoc, MHATokenToKVPool, ReqToTokenPool
+from .model_runner import make_model_runner
 from .radix_attention import AttentionType, RadixAttention
 
 __all__ = [
     "ATTENTION_BACKENDS", "register_attention_backend", "AttentionBackend", "ForwardBatch", "ForwardMode",
-    "KVWriteLoc", "MHATokenToKVPool", "ReqToTokenPool", "AttentionType", "RadixAttention",
+    "KVWriteLoc", "MHATokenToKVPool", "ReqToTokenPool", "AttentionType", "RadixAttention", "make_model_runner",
 ]

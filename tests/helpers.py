@@ -61,17 +61,11 @@ def make_runner(*, device, dtype, pool_dtype, Hq, Hkv, D, page_size, pool_rows, 
                 layer_num=1, v_head_dim=None):
     """A minimal model runner over the mirror pools (what MockModelRunner provides in the reference kit,
     test/kits/attention_unittest/attention_methods/dense_attention.py:306-418)."""
-    from sglang_b200.srt_mirror import MHATokenToKVPool, ReqToTokenPool
+    from sglang_b200.srt_mirror import make_model_runner
 
-    rtp = ReqToTokenPool(size=max_bs, max_context_len=max_context_len, device=device)
-    pool = MHATokenToKVPool(size=pool_rows - page_size, page_size=page_size, dtype=pool_dtype, head_num=Hkv,
-                            head_dim=D, layer_num=layer_num, device=device, v_head_dim=v_head_dim)
-    cfg = SimpleNamespace(
-        num_attention_heads=Hq, num_key_value_heads=Hkv, head_dim=D, context_len=max_context_len,
-        get_num_kv_heads=lambda tp: Hkv // tp, get_max_num_attention_heads=lambda: Hq,
-    )
-    return SimpleNamespace(device=device, dtype=dtype, page_size=page_size, model_config=cfg,
-                           req_to_token_pool=rtp, token_to_kv_pool=pool, sliding_window_size=None)
+    return make_model_runner(device=device, dtype=dtype, pool_dtype=pool_dtype, num_heads=Hq, num_kv_heads=Hkv,
+                             head_dim=D, page_size=page_size, pool_rows=pool_rows, max_bs=max_bs,
+                             max_context_len=max_context_len, layer_num=layer_num, v_head_dim=v_head_dim)
 
 
 def make_forward_batch(c, device):
