@@ -59,6 +59,7 @@ def main():
     ap.add_argument("--json", default="")
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--graph", type=int, default=1, help="time through CUDA-graph replays (1) or eager launches (0)")
+    ap.add_argument("--parity-only", action="store_true")
     a = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
@@ -82,6 +83,22 @@ def main():
             for rep in range(4):                                    # repeated calls reuse buffers and flags
                 got = comm.forward(x, w).clone()
             torch.cuda.synchronize()
+            replayed = False
+            if T <= 128:                                            # the device-side launch counter under graph replay
+                side = torch.cuda.Stream()
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    gr = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(gr, stream=side):
+                        g_out = comm.forward(x, w).clone()
+                        g_out2 = comm.forward(x, w).clone()
+                torch.cuda.current_stream().wait_stream(side)
+                for rep in range(3):
+                    gr.replay()
+                torch.cuda.synchronize()
+                replayed = bool(torch.equal(g_out, got) and torch.equal(g_out2, got))
+                got = g_out2
+                del gr
             err = (got.float().cpu() - want).abs()
             # bf16 ulp is 2^-7 relative; each partial and the final sum may round one ulp either way (fp32 vs
             # float64 accumulation), so allow two ulps of the partials' magnitude and report how many are exact
@@ -91,18 +108,18 @@ def main():
             gathered = [torch.empty_like(got) for _ in range(world)]
             dist.all_gather(gathered, got)
             same = all(torch.equal(gathered[0], t) for t in gathered)
-            ok = ok and good and same
+            ok = ok and good and same and (replayed or T > 128)
             if rank == 0:
                 rec = dict(T=T, N=N, K_shard=K, multicast=bool(mc and comm.multicast),
                            mode={0: "auto", 1: "one-shot", 2: "two-shot"}[mode], max_err=float(err.max()),
                            exact_fraction=round(exact, 5),
-                           within_ulp=good, identical_on_all_ranks=same)
+                           within_ulp=good, identical_on_all_ranks=same, graph_replay=replayed)
                 results["parity"].append(rec)
                 print(json.dumps(rec), flush=True)
             del comm
 
     # ---------------------------------------------------------------- timing: Llama-70B o_proj shard (hidden 8192)
-    for T in (8, 32, 64, 128, 512, 2048):
+    for T in (() if a.parity_only else (8, 32, 64, 128, 512, 2048)):
         N, K = 8192, 8192 // world
         x = (torch.randn(T, K, device="cuda") * 0.5).to(dt)
         # the weights rotate through copies larger than L2, so every GEMM streams them from HBM like a layer stack

@@ -12,6 +12,25 @@ DTYPES = {0: torch.bfloat16, 1: torch.float16, 2: torch.float8_e4m3fn, 3: torch.
 
 # BF16 tolerance of BASELINE.json's north_star: max-abs <= 2e-2 against the FP32-accumulated oracle
 ATOL = 2e-2
+# The contractual bound is absolute; at BASELINE context lengths the outputs themselves are small (N(0,1) values under
+# a near-uniform softmax over L keys have sigma ~ sqrt(e / L) ~ 0.026 at L = 4096), so every oracle comparison ALSO
+# asserts a scale-aware bound: rms(err) / rms(ref) <= 1e-2 (bf16 rounding of P and of the output is ~2e-3).
+REL_RMS = 1e-2
+
+
+def rel_rms(got: torch.Tensor, want: torch.Tensor) -> float:
+    err = (got.double() - want.double()).pow(2).mean().sqrt()
+    return float(err / want.double().pow(2).mean().sqrt().clamp_min(1e-30))
+
+
+def assert_close_scaled(got: torch.Tensor, want: torch.Tensor, what: str = "", atol: float = ATOL,
+                        rel: float = REL_RMS) -> None:
+    """max-abs <= 2e-2 (north_star) AND rms(err)/rms(ref) <= 1e-2; prints both when it fails."""
+    got = got.detach().float().cpu().reshape(want.shape)
+    want = want.detach().float().cpu()
+    max_abs = float((got - want).abs().max()) if want.numel() else 0.0
+    r = rel_rms(got, want) if want.numel() else 0.0
+    assert max_abs <= atol and r <= rel, f"{what}: max-abs {max_abs:.3e} (<= {atol}), rel-rms {r:.3e} (<= {rel})"
 
 
 def from_bits(a: np.ndarray, dtype: torch.dtype) -> torch.Tensor:

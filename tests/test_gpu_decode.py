@@ -3,7 +3,7 @@ Tolerance is BASELINE.json's: max-abs <= 2e-2 against the FP32-accumulated oracl
 import pytest
 import torch
 
-from helpers import ATOL, GoldenAttention, run_backend_on_case, store_dtype
+from helpers import ATOL, GoldenAttention, run_backend_on_case, store_dtype, assert_close_scaled
 from oracle import torch_native_ref as ref
 
 pytestmark = pytest.mark.gpu
@@ -21,8 +21,7 @@ def test_golden_decode(name, kernel):
     out, pool = run_backend_on_case(c, decode_kernel=KERNELS[kernel])
     T = c.q.shape[0]
     got = out.float().cpu().view(T, c.Hq, c.D)
-    err = float((got - c.out_ref_fp32.view(T, c.Hq, c.D)).abs().max())
-    assert err <= ATOL, f"{name}: max-abs {err}"
+    assert_close_scaled(got, c.out_ref_fp32.view(T, c.Hq, c.D), name)
     # the rows this step stored: bit-exact against the reference pool
     loc = c.out_cache_loc
     assert torch.equal(pool.k_buffer[0][loc.cuda()].cpu().view(torch.uint8), c.k_rows_after.view(torch.uint8))
@@ -91,8 +90,7 @@ def test_decode_vs_oracle(shape, dtype, pool_dtype, kernel):
     scale = D**-0.5
     got, _ = _run_ops_decode(q, kp, vp, rtt, rpi, seq, scale, pool_dtype, kernel=KERNELS[kernel])
     want = ref.decode_ref(q, kp, vp, rtt, rpi, seq, scale, kv_dtype=pool_dtype)
-    err = float((got - want).abs().max())
-    assert err <= ATOL, f"max-abs {err}"
+    assert_close_scaled(got, want)
 
 
 def test_decode_fp8_descale_and_logit_cap():
@@ -101,10 +99,10 @@ def test_decode_fp8_descale_and_logit_cap():
     scale = 128**-0.5
     got, _ = _run_ops_decode(q, kp, vp, rtt, rpi, seq, scale, torch.float8_e4m3fn, k_scale=0.5, v_scale=1.75)
     want = ref.decode_ref(q, kp, vp, rtt, rpi, seq, scale, kv_dtype=torch.float8_e4m3fn, k_scale=0.5, v_scale=1.75)
-    assert float((got - want).abs().max()) <= ATOL
+    assert_close_scaled(got, want)
     got, _ = _run_ops_decode(q, kp, vp, rtt, rpi, seq, scale, torch.float8_e4m3fn, logit_cap=5.0)
     want = ref.decode_ref(q, kp, vp, rtt, rpi, seq, scale, kv_dtype=torch.float8_e4m3fn, logit_cap=5.0)
-    assert float((got - want).abs().max()) <= ATOL
+    assert_close_scaled(got, want)
 
 
 @pytest.mark.parametrize("idx_dtype", [torch.int32, torch.int64])
@@ -119,4 +117,4 @@ def test_split_invariance_and_index_dtypes(idx_dtype):
     assert int(ws_a.plan[1]) == sum((L + 63) // 64 for L in [1000, 64, 63, 2500]) and int(ws_b.plan[1]) == 4
     assert float((a - b).abs().max()) <= 4e-3
     want = ref.decode_ref(q, kp, vp, rtt, rpi, seq, scale)
-    assert float((a - want).abs().max()) <= ATOL
+    assert_close_scaled(a, want)

@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import ATOL, make_runner
+from helpers import ATOL, make_runner, assert_close_scaled
 from oracle import torch_native_ref as ref
 
 pytestmark = pytest.mark.gpu
@@ -102,7 +102,7 @@ def test_cfg2_full_size_properties(pool_dtype):
     sub = [0, 17, 40, 63]
     want = ref.decode_ref(q[sub].cpu(), kp.cpu(), vp.cpu(), rtt.cpu(), rpi[sub].cpu(), seq[sub].cpu(), scale,
                           kv_dtype=pool_dtype)
-    assert float((o[sub].float().cpu() - want).abs().max()) <= ATOL
+    assert_close_scaled(o[sub].float().cpu(), want)
     p = torch.randperm(bs, device="cuda")
     o_perm = run(rpi[p], q[p])
     assert torch.equal(o_perm, o[p])
@@ -173,6 +173,6 @@ def test_cuda_graph_capture_and_replay():
         got = s_out[:raw_bs].float().cpu().view(raw_bs, Hq, D)
         want = ref.decode_ref(q.view(raw_bs, Hq, D), pool.k_buffer[0].cpu(), pool.v_buffer[0].cpu(),
                               rtp.req_to_token.cpu(), torch.arange(1, raw_bs + 1), torch.tensor(lens), D**-0.5)
-        assert float((got - want).abs().max()) <= ATOL
+        assert_close_scaled(got, want)
         assert torch.equal(pool.k_buffer[0][loc].cpu().view(raw_bs, -1), k)  # new rows stored by the replay
         assert int(pool.k_buffer[0][0].abs().sum()) == 0                     # slot-0 sink never written

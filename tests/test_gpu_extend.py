@@ -2,7 +2,7 @@
 import pytest
 import torch
 
-from helpers import ATOL, GoldenAttention, run_backend_on_case, store_dtype
+from helpers import ATOL, GoldenAttention, run_backend_on_case, store_dtype, assert_close_scaled
 from oracle import torch_native_ref as ref
 
 pytestmark = pytest.mark.gpu
@@ -19,8 +19,7 @@ def test_golden_extend(name, kernel):
     out, pool = run_backend_on_case(c, extend_kernel=KERNELS[kernel])
     T = c.q.shape[0]
     got = out.float().cpu().view(T, c.Hq, c.D)
-    err = float((got - c.out_ref_fp32.view(T, c.Hq, c.D)).abs().max())
-    assert err <= ATOL, f"{name}: max-abs {err}"
+    assert_close_scaled(got, c.out_ref_fp32.view(T, c.Hq, c.D), name)
     loc = c.out_cache_loc
     assert torch.equal(pool.k_buffer[0][loc.cuda()].cpu().view(torch.uint8), c.k_rows_after.view(torch.uint8))
     assert torch.equal(pool.v_buffer[0][loc.cuda()].cpu().view(torch.uint8), c.v_rows_after.view(torch.uint8))
@@ -96,8 +95,7 @@ def test_extend_vs_oracle(shape, dtype, pool_dtype, kernel):
     scale = D**-0.5
     got, _ = run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, kernel=KERNELS[kernel])
     want = ref.extend_ref(q, kp, vp, rtt, rpi, pre, ext, scale, kv_dtype=pool_dtype)
-    err = float((got - want).abs().max())
-    assert err <= ATOL, f"max-abs {err}"
+    assert_close_scaled(got, want)
 
 
 def test_fast_path_covers_d64_and_d128():
@@ -116,7 +114,7 @@ def test_extend_non_causal_and_lse():
     scale = 128**-0.5
     got, _ = run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, torch.bfloat16, causal=False)
     want = ref.extend_ref(q, kp, vp, rtt, rpi, pre, ext, scale, causal=False)
-    assert float((got - want).abs().max()) <= ATOL
+    assert_close_scaled(got, want)
     # LSE (natural log) of the causal scores, as chunked-prefix merging consumes it
     _, lse = run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, torch.bfloat16, want_lse=True)
     t = 0

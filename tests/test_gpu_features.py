@@ -8,7 +8,7 @@ from types import SimpleNamespace
 import pytest
 import torch
 
-from helpers import ATOL, GoldenFeatures, make_runner
+from helpers import ATOL, GoldenFeatures, make_runner, assert_close_scaled
 from oracle import torch_native_ref as ref
 from test_gpu_decode import _random_problem
 from test_gpu_extend import make_extend_problem
@@ -84,7 +84,7 @@ def test_golden_features(name):
                                         sinks=c.sinks, custom_mask=c.custom_mask, mask_indptr=c.mask_indptr,
                                         mask_skip_prefix=c.mask_skip_prefix, want_lse=True)
         assert float((lse - want_lse).abs().max()) <= ATOL, name
-    assert float((got - want).abs().max()) <= ATOL, name
+    assert_close_scaled(got, want, name)
     # and against what the reference itself produced in float32 (the reference kit's own tolerance, 3e-2)
     assert float((got - c.out.view_as(got)).abs().max()) <= 3e-2, name
 
@@ -117,11 +117,11 @@ def test_decode_options(shape, opts, pool_dtype):
     want, want_lse = ref.decode_ref(q, kp, vp, rtt, rpi, seq, scale, kv_dtype=pool_dtype, want_lse=True, **kw)
     for kernel in (0, 1):
         got, lse = _decode(q, kp, vp, rtt, rpi, seq, scale, pool_dtype, kernel=kernel, want_lse=True, **kw)
-        assert float((got - want).abs().max()) <= ATOL, f"kernel {kernel}"
+        assert_close_scaled(got, want, f"kernel {kernel}")
         assert float((lse - want_lse).abs().max()) <= ATOL, f"kernel {kernel} lse"
     # the split must not matter (windowed ranges start mid-request: chunk starts are not 16-aligned)
     got64, lse64 = _decode(q, kp, vp, rtt, rpi, seq, scale, pool_dtype, fixed_chunk=64, want_lse=True, **kw)
-    assert float((got64 - want).abs().max()) <= ATOL
+    assert_close_scaled(got64, want)
     assert float((lse64 - want_lse).abs().max()) <= ATOL
 
 
@@ -152,7 +152,7 @@ def test_extend_options(shape, opts, pool_dtype):
     want, want_lse = ref.extend_ref(q, kp, vp, rtt, rpi, pre, ext, scale, kv_dtype=pool_dtype, want_lse=True, **kw)
     for kernel in (0, 1):
         got, lse = _extend(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, kernel=kernel, want_lse=True, **kw)
-        assert float((got - want).abs().max()) <= ATOL, f"kernel {kernel}"
+        assert_close_scaled(got, want, f"kernel {kernel}")
         assert float((lse - want_lse).abs().max()) <= ATOL, f"kernel {kernel} lse"
 
 
@@ -180,7 +180,7 @@ def test_extend_custom_mask_large(Hq, Hkv, D, pool_dtype):
             for kernel in (0, 1):
                 got, lse = _extend(q, kp, vp, rtt, rpi, pre, ext, D ** -0.5, pool_dtype, kernel=kernel,
                                    want_lse=True, **kw)
-                assert float((got - want).abs().max()) <= ATOL, f"skip_prefix={skip} window={window} kernel={kernel}"
+                assert_close_scaled(got, want, f"skip_prefix={skip} window={window} kernel={kernel}")
                 assert float((lse - want_lse).abs().max()) <= ATOL, f"lse skip_prefix={skip} kernel={kernel}"
 
 
@@ -203,7 +203,7 @@ def test_merge_state_golden_and_random():
     big = torch.empty(T, H + 3, D, dtype=torch.bfloat16, device="cuda")       # strided output view
     out, lse = ops.merge_state(oa.cuda(), la.cuda(), ob.cuda(), lb.cuda(), out=big[:, 1 : H + 1])
     want, want_lse = ref.merge_state_ref(oa, la, ob, lb)
-    assert float((out.float().cpu() - want).abs().max()) <= ATOL
+    assert_close_scaled(out.float().cpu(), want)
     assert float((lse.cpu() - want_lse).abs().max()) <= 1e-5
 
 
@@ -236,7 +236,7 @@ def test_chunked_prefix_equals_one_pass():
         o_a[t0 : t0 + E], lse_a[t0 : t0 + E] = oo, ll
         t0 += E
     out, lse = ops.merge_state(o_a.bfloat16().cuda(), lse_a.cuda(), o_b.bfloat16().cuda(), lse_b.cuda())
-    assert float((out.float().cpu() - full).abs().max()) <= ATOL
+    assert_close_scaled(out.float().cpu(), full)
     assert float((lse.cpu() - full_lse).abs().max()) <= ATOL
 
 
@@ -299,7 +299,7 @@ def test_backend_hybrid_sliding_window(Hq, Hkv, D):
                     fb, pb.backend, **fkw)
         torch.cuda.synchronize()
         want = ref.decode_ref(pb.q, pb.kp, pb.vp, pb.rtt, pb.rpi, seq, scale, **kw)
-        assert float((out.float().cpu().view_as(want) - want).abs().max()) <= ATOL, f"decode layer {layer.layer_id}"
+        assert_close_scaled(out.float().cpu().view_as(want), want, f"decode layer {layer.layer_id}")
     # ---- extend
     prefix, ext = [300, 0, 130], [200, 129, 3]
     pb = _backend_problem(Hq, Hkv, D, prefix, ext, sliding_window=W, seed=D + 1)
@@ -317,7 +317,7 @@ def test_backend_hybrid_sliding_window(Hq, Hkv, D):
                     fb, pb.backend, **fkw)
         torch.cuda.synchronize()
         want = ref.extend_ref(pb.q, pb.kp, pb.vp, pb.rtt, pb.rpi, pre_t, ext_t, scale, **kw)
-        assert float((out.float().cpu().view_as(want) - want).abs().max()) <= ATOL, f"extend layer {layer.layer_id}"
+        assert_close_scaled(out.float().cpu().view_as(want), want, f"extend layer {layer.layer_id}")
 
 
 def test_backend_target_verify_and_lse():
@@ -351,7 +351,7 @@ def test_backend_target_verify_and_lse():
     want, want_lse = ref.extend_ref(pb.q, pb.kp, pb.vp, pb.rtt, pb.rpi, torch.tensor(prefix), torch.tensor([n] * 3),
                                     D ** -0.5, custom_mask=mask.to(torch.uint8), mask_indptr=indptr, want_lse=True)
     assert tuple(out.shape) == (pb.T, Hq, D) and tuple(lse.shape) == (pb.T, Hq)
-    assert float((out.float().cpu() - want).abs().max()) <= ATOL
+    assert_close_scaled(out.float().cpu(), want)
     assert float((lse.cpu() - want_lse).abs().max()) <= ATOL
 
 
@@ -408,4 +408,4 @@ def test_backend_swa_decode_cuda_graph():
         for layer, out, kw in ((layers[0], outs[0], dict(window_keys=W + 1)), (layers[1], outs[1], {})):
             want = ref.decode_ref(pb.q, kp, vp, pb.rtt, pb.rpi, seq, scale, **kw)
             got = out[: pb.bs].float().cpu().view_as(want)
-            assert float((got - want).abs().max()) <= ATOL, f"replay {it} layer {layer.layer_id}"
+            assert_close_scaled(got, want, f"replay {it} layer {layer.layer_id}")

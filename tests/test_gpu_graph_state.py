@@ -12,7 +12,7 @@ from types import SimpleNamespace
 import pytest
 import torch
 
-from helpers import ATOL
+from helpers import ATOL, assert_close_scaled
 from oracle import torch_native_ref as ref
 from test_gpu_features import _backend_problem
 
@@ -39,7 +39,7 @@ def test_graph_state_smaller_than_eager_batch():
                 fb, be)
     torch.cuda.synchronize()
     want = ref.decode_ref(pb.q, pb.kp, pb.vp, pb.rtt, pb.rpi, torch.tensor(pb.lens, dtype=torch.int32), D ** -0.5)
-    assert float((out.float().cpu().view_as(want) - want).abs().max()) <= ATOL
+    assert_close_scaled(out.float().cpu().view_as(want), want)
 
 
 def _tree_mask(prefix, n, seed):
@@ -115,7 +115,7 @@ def test_target_verify_graph_replay_with_new_mask_and_interleaved_prefill():
     torch.cuda.synchronize()
     want2 = ref.extend_ref(pb2.q, pb2.kp, pb2.vp, pb2.rtt, pb2.rpi, torch.tensor(big_prefix), torch.tensor(big_ext),
                            scale)
-    assert float((out2.float().cpu().view_as(want2) - want2).abs().max()) <= ATOL
+    assert_close_scaled(out2.float().cpu().view_as(want2), want2)
     be.req_to_token_pool, be.token_to_kv_pool = pb.runner.req_to_token_pool, pb.runner.token_to_kv_pool
 
     # ---- replays: 3 live requests in a batch padded to 4, a different tree mask every time
@@ -137,4 +137,4 @@ def test_target_verify_graph_replay_with_new_mask_and_interleaved_prefill():
         want = ref.extend_ref(pb.q, pb.kp, pb.vp, pb.rtt, pb.rpi, torch.tensor(prefix), torch.tensor([n] * bs),
                               scale, custom_mask=mask.to(torch.uint8), mask_indptr=indptr)
         got = out_buf[: bs * n].float().cpu().view_as(want)
-        assert float((got - want).abs().max()) <= ATOL, f"replay {it}"
+        assert_close_scaled(got, want, f"replay {it}")
