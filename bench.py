@@ -312,8 +312,8 @@ class DecodeStep:
                     be.init_forward_metadata_in_graph(self.fb)
                 for l in rng:
                     o = self.layer(l, oproj=oproj)
-                    if keep_outputs:
-                        outs.append(o)
+                    if keep_outputs:         # the fused o_proj returns a view of its (reused) symmetric buffer
+                        outs.append(o.clone() if self.comm is not None and oproj else o)
                 out = torch.stack(outs) if keep_outputs else None        # one D2H copy per segment
             launches = ops.launch_count - n0
         torch.cuda.current_stream().wait_stream(side)
