@@ -9,6 +9,9 @@
 // stored into the pool before this launch, so prefix and new K/V are both read through
 // the page table, exactly like the torch_native oracle.
 // Algorithmic FLOPs per launch: 4 * Hq * D * sum_r (E_r * P_r + E_r * (E_r + 1) / 2).
+#include <cuda.h>   // CUtensorMap types only; the encoder is resolved through cudaGetDriverEntryPoint
+
+#include <cstring>
 #include <type_traits>
 
 #include "common.cuh"
@@ -117,6 +120,7 @@ struct ExtendParams {
   int32_t window_keys;          // query at position x attends (x - window_keys, x]; 0 = off
   int32_t mask_skip_prefix;
   int32_t kv_e5m2;              // FP8 pool bytes are e5m2 (else e4m3); read by the tcgen05 kernel's FP8 producers only
+  int32_t pool_slots;           // rows of the pool buffers (TMA: a row index >= pool_slots is zero-filled)
   float sm_scale, k_scale, v_scale, logit_cap;
   const float* sinks;           // [Hq] natural-log sink logits or nullptr
   const uint8_t* custom_mask;   // see b200_extend_args
@@ -267,6 +271,7 @@ extern "C" int b200attn_extend(const b200_extend_args* a, b200_stream_t stream_)
   p.window_keys = a->window_keys > 0 ? a->window_keys : 0; p.sinks = a->sinks;
   p.custom_mask = a->custom_mask; p.mask_indptr = a->mask_indptr; p.mask_skip_prefix = a->mask_skip_prefix;
   p.kv_e5m2 = a->kv_dtype == B200_FP8_E5M2;
+  p.pool_slots = a->pool_slots > 0 && a->pool_slots < 0x7fffffff ? (int32_t)a->pool_slots : 0;
   B200_CHECK_ARG(a->custom_mask == nullptr || a->mask_indptr != nullptr, "extend: custom_mask needs mask_indptr");
   B200_CHECK_ARG(!(p.window_keys > 0 && !a->causal), "extend: a sliding window needs causal attention");
 

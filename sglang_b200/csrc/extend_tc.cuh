@@ -17,19 +17,25 @@
 //   warps 4-7    the same for query tile 1
 //   warp  8      TMEM allocation + MMA issue (warp-uniform control flow, one elected lane issues)
 //   warps 9-11   idle (they only give their registers away)
-//   warps 12-15  producers: page-table gather of K/V rows (and Q once) with 16-byte cp.async into
-//                128B-swizzled tiles; completion is signalled by cp.async.mbarrier.arrive, so the
-//                producers never wait for their own loads
+//   warps 12-15  producers.  Q once, with 16-byte cp.async into 128B-swizzled tiles.  K/V ring:
+//                * 16-bit pools (kTma): ONE warp issues TMA `cp.async.bulk.tensor.2d.tile::gather4` -- four
+//                  page-table rows per instruction, hardware 128B swizzle, completion counted in bytes on the
+//                  slot's mbarrier; 128 instructions fill a K + V block pair, no generic-proxy fence needed
+//                * FP8 pools / strided pools: page-table gather with cp.async by all four warps (FP8 bytes are
+//                  widened to f16 on the way), completion by cp.async.mbarrier.arrive
 //
 // TMEM (512 columns): S0 [0,128)  S1 [128,256)  O0 [256,384)  O1 [384,512);  P_t = S_t columns [0,64).
 // Shared memory: Q0,Q1 32 KiB each | ring of 5 x 32 KiB slots filled K0 V0 K1 V1 ... | barriers.
 
 
-// Timing-aid ablations (never defined in the shipped build): skip the ring refills / the exponentials.
-#ifndef B200_ABLATE_FILL
+// Timing-aid ablations exist only in -DB200_DEV builds (benchmarks/_ab/build_variant.sh): skip the ring refills /
+// the exponentials.  The shipped library compiles neither.
+#if !defined(B200_DEV) || !defined(B200_ABLATE_FILL)
+#undef B200_ABLATE_FILL
 #define B200_ABLATE_FILL 0
 #endif
-#ifndef B200_ABLATE_EXP
+#if !defined(B200_DEV) || !defined(B200_ABLATE_EXP)
+#undef B200_ABLATE_EXP
 #define B200_ABLATE_EXP 0
 #endif
 
@@ -57,6 +63,9 @@ constexpr int kTmemCols = 512;
 constexpr int kTmemS = 0, kTmemO = 256;
 
 constexpr int kRegsSoftmax = 200, kRegsOther = 56;   // 256 x 200 + 256 x 56 = 64 Ki registers
+// Of every 8 column pairs, this many take the polynomial exp2 on the FMA pipe instead of MUFU.EX2 (16/clk/SM would
+// otherwise cost as many cycles as the MMAs); tuned on B200, both paths agree to 1e-4 relative.
+constexpr int kEmuEighths = 3;
 
 // Shared-memory map and barrier slots.  16-bit pools: 5 ring slots.  FP8 pools: 4 ring slots (the MMA
 // operands are f16 tiles the producers write) + 2 raw 16 KiB landing buffers for the cp.async gathers.
@@ -97,8 +106,12 @@ __device__ __forceinline__ uint32_t swz_off(int row, int chunk, int rows) {
 // never touches the second 64-wide d half: the producers fill 128-byte rows, QK runs 4 k-steps instead of 8, PV is
 // an M128 x N64 MMA into 64 O columns.  (Its softmax cost per kv block is the same as for D = 128, so it is
 // exp-bound rather than MMA-bound.)
-template <typename QT, int kEmu, bool kFp8, bool kOpts, int kHD>
-__global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const ExtendParams p, const int max_tiles) {
+// kTma: the K/V ring is filled by TMA gather4 through the two tensor maps (16-bit pools with contiguous heads).
+template <typename QT, int kEmu, bool kFp8, bool kOpts, int kHD, bool kTma>
+__global__ void __launch_bounds__(tc::kThreads, 1)
+extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constant__ CUtensorMap tm_k,
+                 const __grid_constant__ CUtensorMap tm_v) {
+  static_assert(!(kTma && kFp8), "the FP8 producers widen bytes themselves");
   using namespace tc;
   using namespace ptx;
   using L = Layout<kFp8>;
@@ -142,7 +155,7 @@ __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const Extend
   if (threadIdx.x == 0) {
     mbar_init(bar(kBarQFull), kProducerThreads);
     for (int s = 0; s < kSlots; ++s) {
-      mbar_init(bar(kBarFull + s), kProducerThreads);
+      mbar_init(bar(kBarFull + s), kTma ? 1 : kProducerThreads);
       mbar_init(bar(kBarEmpty + s), 1);
     }
     for (int t = 0; t < kQTiles; ++t) {
@@ -163,6 +176,8 @@ __global__ void __launch_bounds__(tc::kThreads, 1) extend_tc_kernel(const Extend
     setmaxnreg_dec<kRegsOther>();
     if constexpr (kFp8) {
 #include "extend_tc_producer_fp8.inc"
+    } else if constexpr (kTma) {
+#include "extend_tc_producer_tma.inc"
     } else {
 #include "extend_tc_producer.inc"
     }
@@ -204,42 +219,85 @@ bool extend_fast_layout_ok(const ExtendParams& p, int kv_dtype) {
          p.k_stride_s > 0 && p.v_stride_s > 0 && p.k_stride_s < (1ll << 30) && p.v_stride_s < (1ll << 30);
 }
 
-template <typename QT, int kEmu, bool kFp8, bool kOpts, int kHD>
+// ---- TMA descriptors (host) -------------------------------------------------------------------------------------
+// The pool buffer [slots, Hkv * D] as a 2-D tensor of 16-bit words; box = 64 words x 1 row, SWIZZLE_128B: a gather4
+// lands four 128-byte rows exactly where the UMMA descriptors of this kernel expect them.  cuTensorMapEncodeTiled is
+// resolved through the runtime (no link-time dependency on libcuda).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn tensor_map_encoder() {
+  static std::atomic<void*> cached{nullptr};
+  void* fn = cached.load(std::memory_order_acquire);
+  if (fn == nullptr) {
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    cached.store(fn, std::memory_order_release);
+  }
+  return reinterpret_cast<EncodeTiledFn>(fn);
+}
+
+// rows x width 16-bit words, row pitch `stride_elems` words
+bool make_pool_tensor_map(CUtensorMap* tm, const void* base, int64_t rows, int64_t width, int64_t stride_elems) {
+  EncodeTiledFn enc = tensor_map_encoder();
+  if (enc == nullptr) return false;
+  const cuuint64_t gdim[2] = {(cuuint64_t)width, (cuuint64_t)rows};
+  const cuuint64_t gstride[1] = {(cuuint64_t)stride_elems * 2};
+  const cuuint32_t box[2] = {64, 1};
+  const cuuint32_t estr[2] = {1, 1};
+  return enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// TMA needs: heads contiguous inside a pool row, 16-byte aligned base and row pitch, row ids that fit int32
+bool extend_tma_ok(const ExtendParams& p, const b200_extend_args& a) {
+  return p.k_stride_h == p.head_dim_qk && p.v_stride_h == p.head_dim_v && a.pool_slots > 0 &&
+         a.pool_slots < 0x7fffffff && p.k_stride_s % 8 == 0 && p.v_stride_s % 8 == 0 &&
+         p.k_stride_s >= (int64_t)p.num_kv_heads * p.head_dim_qk && p.v_stride_s >= (int64_t)p.num_kv_heads * p.head_dim_v;
+}
+
+template <typename QT, bool kFp8, bool kOpts, int kHD, bool kTma>
 int launch_extend_fast_t(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   static std::atomic<uint64_t> configured{0};
   constexpr int kSmem = tc::Layout<kFp8>::kSmemBytes;
-  auto kern = extend_tc_kernel<QT, kEmu, kFp8, kOpts, kHD>;
+  auto kern = extend_tc_kernel<QT, tc::kEmuEighths, kFp8, kOpts, kHD, kTma>;
   B200_CHECK_CUDA(set_max_dynamic_smem(kern, kSmem, configured));
+  CUtensorMap tm_k, tm_v;
+  memset(&tm_k, 0, sizeof(tm_k));
+  memset(&tm_v, 0, sizeof(tm_v));
+  if (kTma) {
+    const bool ok = make_pool_tensor_map(&tm_k, p.k_cache, a.pool_slots, (int64_t)p.num_kv_heads * kHD, p.k_stride_s) &&
+                    make_pool_tensor_map(&tm_v, p.v_cache, a.pool_slots, (int64_t)p.num_kv_heads * kHD, p.v_stride_s);
+    if (!ok) {
+      set_error("extend: cuTensorMapEncodeTiled failed for the KV pool (%lld slots)", (long long)a.pool_slots);
+      return B200_ECUDA;
+    }
+  }
   const int block_q = extend_fast_block_q(p.group);
   // host-side bound on the number of work items: sum_r ceil(E_r / block_q) <= T / block_q + bs
   int64_t tiles = a.num_q_tokens / block_q + a.batch_size;
   if (tiles > a.max_tiles) tiles = a.max_tiles;
   const int64_t grid = tiles * p.num_kv_heads;
   B200_CHECK_ARG(grid > 0 && grid < 0x7fffffff, "extend: bad grid %lld", (long long)grid);
-  kern<<<(unsigned)grid, tc::kThreads, kSmem, stream>>>(p, (int)tiles);
+  kern<<<(unsigned)grid, tc::kThreads, kSmem, stream>>>(p, (int)tiles, tm_k, tm_v);
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;
-}
-
-// Share of exp2 evaluated by the polynomial (eighths): 3 is the tuned default, B200ATTN_EXTEND_EMU=0 turns the
-// polynomial off (A/B aid; both paths are within 1e-4 relative of each other).
-int extend_emu_eighths() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("B200ATTN_EXTEND_EMU");
-    v = (e && atoi(e) == 0) ? 0 : 3;
-  }
-  return v;
 }
 
 template <typename QT, bool kFp8, int kHD>
 int launch_extend_fast_d(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr || p.custom_mask != nullptr;
-  if (extend_emu_eighths() == 0)
-    return opts ? launch_extend_fast_t<QT, 0, kFp8, true, kHD>(p, a, stream)
-                : launch_extend_fast_t<QT, 0, kFp8, false, kHD>(p, a, stream);
-  return opts ? launch_extend_fast_t<QT, 3, kFp8, true, kHD>(p, a, stream)
-              : launch_extend_fast_t<QT, 3, kFp8, false, kHD>(p, a, stream);
+  if constexpr (!kFp8) {
+    if (extend_tma_ok(p, a))
+      return opts ? launch_extend_fast_t<QT, false, true, kHD, true>(p, a, stream)
+                  : launch_extend_fast_t<QT, false, false, kHD, true>(p, a, stream);
+  }
+  return opts ? launch_extend_fast_t<QT, kFp8, true, kHD, false>(p, a, stream)
+              : launch_extend_fast_t<QT, kFp8, false, kHD, false>(p, a, stream);
 }
 
 template <typename QT, bool kFp8>

@@ -103,6 +103,28 @@ __device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
 
+// ------------------------------------------------------------------ TMA (cp.async.bulk.tensor)
+// One arrival + `bytes` of expected transaction count: the phase completes when the TMA copies that name this
+// barrier have delivered that many bytes.
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// tile::gather4 (sm_100): FOUR arbitrary rows r0..r3 of a 2-D tensor, box-width elements starting at column c0,
+// land as four consecutive box rows at `dst` (hardware 128B swizzle from the tensor map); a row index outside the
+// tensor is zero-filled.  Completion is counted in bytes on `bar`.  The page-table gather of a token-granular KV
+// pool costs one instruction per 4 tokens instead of one LDGSTS per 16 bytes.
+__device__ __forceinline__ void tma_gather4(uint32_t dst, const void* tmap, uint32_t bar, int c0, int r0, int r1,
+                                            int r2, int r3) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile::gather4.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(r0), "r"(r1), "r"(r2), "r"(r3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");
+}
+
 // ------------------------------------------------------------------ register re-allocation between warpgroups
 template <int N> __device__ __forceinline__ void setmaxnreg_inc() {
   asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
