@@ -150,7 +150,7 @@ def extend_compare(name, bs, P, E, Hq, Hkv, D, iters=5):
     pre = torch.full((bs,), P, dtype=torch.int32, device=dev)
     ext = torch.full((bs,), E, dtype=torch.int32, device=dev)
     sm, _, _ = ops.device_info()
-    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, torch.bfloat16, 0)
+    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, torch.bfloat16, 0, num_tokens=T, batch_size=bs)
     ws = ops.ExtendWorkspace.create(bs, T // bq + bs + 1, dev, num_ctas=sm)
     ops.extend_plan(ws, ext, bq)
 
@@ -232,7 +232,7 @@ def extend_compare_blackwell(name, bs, P, E, Hq, Hkv, D, page, iters=5):
     pre = torch.full((bs,), P, dtype=torch.int32, device=dev)
     ext = torch.full((bs,), E, dtype=torch.int32, device=dev)
     sm, _, _ = ops.device_info()
-    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, torch.bfloat16, 0)
+    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, torch.bfloat16, 0, num_tokens=T, batch_size=bs)
     ws = ops.ExtendWorkspace.create(bs, T // bq + bs + 1, dev, num_ctas=sm)
     ops.extend_plan(ws, ext, bq)
 

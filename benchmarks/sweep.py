@@ -118,7 +118,7 @@ def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_d
     pre = torch.full((bs,), P, dtype=torch.int32, device=dev)
     ext = torch.full((bs,), E, dtype=torch.int32, device=dev)
     sm, _, _ = ops.device_info()
-    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, pool_dtype, kernel)
+    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, pool_dtype, kernel, num_tokens=T, batch_size=bs)
     ws = ops.ExtendWorkspace.create(bs, T // bq + bs + 1, dev, num_ctas=sm)
     ops.extend_plan(ws, ext, bq)
 

@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 3
+#define B200ATTN_ABI_VERSION 4
 
 typedef void* b200_stream_t; /* a cudaStream_t */
 
@@ -252,6 +252,11 @@ typedef struct b200_extend_args {
                                    != 0.  Replaces the causal rule on the new tokens (x >= P_r); NULL = none */
   const int64_t* mask_indptr;   /* [bs + 1] offsets into custom_mask */
   int32_t mask_skip_prefix;     /* 1: prefix positions (x < P_r) are always visible (SKIP_PREFIX_CUSTOM_MASK) */
+  int32_t block_q;              /* the block_q the plan was built with (b200attn_extend_block_q2): selects the
+                                   one-CTA or the CTA-pair tcgen05 kernel; 0 = the one-CTA value */
+  int32_t page_size;            /* KV page size of the pool (req_to_token entries of one page are consecutive slots,
+                                   pages are page_size-aligned); >= 16 lets the fill use one TMA box per page; 0/1 =
+                                   token-granular */
 } b200_extend_args;
 
 int b200attn_extend(const b200_extend_args* args, b200_stream_t stream);
@@ -260,6 +265,11 @@ int b200attn_extend_fast_supported(int32_t head_dim_qk, int32_t head_dim_v, int3
 /* query tokens per tile the kernel that would be picked uses (for the plan) */
 int b200attn_extend_block_q(int32_t head_dim_qk, int32_t head_dim_v, int32_t group,
                             int32_t q_dtype, int32_t kv_dtype, int32_t kernel);
+/* the same, given the host-known size of the forward (sum E_r, batch size): requests that extend by more than one
+ * CTA's worth of query tokens on average are planned for the CTA-pair kernel (D = 128, 16-bit pool), whose work
+ * items are twice as large.  Pass the result to b200attn_extend_plan and in b200_extend_args.block_q. */
+int b200attn_extend_block_q2(int32_t head_dim_qk, int32_t head_dim_v, int32_t group, int32_t q_dtype,
+                             int32_t kv_dtype, int32_t kernel, int64_t num_q_tokens, int32_t batch_size);
 
 /* ------------------------------------------------------------------------ *
  * Fused rotary embedding + KV-store (the step right before RadixAttention.forward).

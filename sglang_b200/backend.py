@@ -138,8 +138,11 @@ class B200AttnBackend(_Base):
         self._ext_lens = None          # (prefix_lens, extend_lens, custom_mask, mask_indptr) of this forward
         self._graph_state_frozen = False
         group = self.num_head // self.num_kv_head
-        self._extend_block_q = ops.extend_block_q(self.head_dim, self.v_head_dim, group, self._q_dtype,
-                                                  self.kv_dtype, self.extend_kernel)
+        # smallest work item any extend kernel uses (sizes the work lists); the per-forward value is chosen in
+        # init_forward_metadata_out_graph from the forward's size
+        self._extend_min_block_q = ops.extend_block_q(self.head_dim, self.v_head_dim, group, self._q_dtype,
+                                                      self.kv_dtype, self.extend_kernel)
+        self._extend_block_q = self._extend_min_block_q
         self.num_draft_tokens = _spec_num_draft_tokens(model_runner)
         self.forward_metadata = None
         #: optional (start, stop) torch.cuda.Event pair re-recorded around the next decode attention kernel
@@ -176,7 +179,7 @@ class B200AttnBackend(_Base):
         a replay) gets the same set back, so the replay refills exactly the buffers the graph reads.  Sets that a
         graph holds are never reallocated or freed; other eager batches use the graph set when they
         fit it, else a separate eager set that grows geometrically."""
-        tiles = tokens // self._extend_block_q + bs + 1
+        tiles = tokens // self._extend_min_block_q + bs + 1
         st = self._ext_captured.get(key)
         if st is not None and st.fits(bs, tiles, mask_bytes):
             return st
@@ -253,6 +256,7 @@ class B200AttnBackend(_Base):
                 torch.cumsum((pre.to(torch.int64) + n) * n, dim=0, out=mask_indptr[1:])
                 mask = st.mask
             self._ext, self._ext_lens = st, (pre, ext, mask, mask_indptr)
+            self._pick_block_q(bs * n, bs)
         elif not eager_lens and mode.is_draft_extend_v2():
             # CUDA-graph draft-extend: a fixed number of query rows per request; the cached prefix is
             # seq_lens - accepted tokens, clamped for padded rows (triton_backend.py:529-565)
@@ -270,12 +274,19 @@ class B200AttnBackend(_Base):
             else:
                 pre.copy_(seq)
             self._ext, self._ext_lens = st, (pre, ext, None, None)
+            self._pick_block_q(bs * n, bs)
         else:
             T = getattr(forward_batch, "extend_num_tokens", None)
             if T is None:
                 T = forward_batch.out_cache_loc.shape[0]
             self._ext = self._select_ext((int(mode), bs), bs, int(T), 0, in_capture)
             self._ext_lens = (forward_batch.extend_prefix_lens, forward_batch.extend_seq_lens, None, None)
+            self._pick_block_q(int(T), bs)
+
+    def _pick_block_q(self, tokens: int, bs: int) -> None:
+        self._extend_block_q = ops.extend_block_q(self.head_dim, self.v_head_dim, self.num_head // self.num_kv_head,
+                                                  self._q_dtype, self.kv_dtype, self.extend_kernel,
+                                                  num_tokens=int(tokens), batch_size=int(bs))
 
     def init_forward_metadata_in_graph(self, forward_batch):
         """One planner launch (static shape, graph-recordable, no host sync, reads persistent buffers only)."""
@@ -308,7 +319,7 @@ class B200AttnBackend(_Base):
                 waves=self.DECODE_WAVES)
             self.decode_ws_swa = self._swa_workspace(self.decode_ws)
         g = self._ext_graph
-        tiles = max_num_tokens // self._extend_block_q + max_bs + 1
+        tiles = max_num_tokens // self._extend_min_block_q + max_bs + 1
         # custom (tree) masks of TARGET_VERIFY: draft tokens x (context + draft tokens) bytes per request, the
         # reference's bound (triton_backend.py:1013-1017)
         mask_bytes = max_num_tokens * self.max_context_len if self.num_draft_tokens > 0 else 0
@@ -437,7 +448,7 @@ class B200AttnBackend(_Base):
             logit_cap=self._logit_cap(layer), causal=causal,
             kernel=self.extend_kernel, lse=lse,
             window_keys=self._window_keys(layer) if causal else 0, sinks=self._sinks(kwargs, q.device),
-            custom_mask=custom_mask, mask_indptr=mask_indptr, mask_skip_prefix=True,
+            custom_mask=custom_mask, mask_indptr=mask_indptr, mask_skip_prefix=True, page_size=self.page_size,
         )
         if lse is not None:
             return o.view(T, layer.tp_q_head_num, layer.v_head_dim), lse

@@ -237,6 +237,17 @@ extern "C" int b200attn_extend_block_q(int32_t dqk, int32_t dv, int32_t group, i
   return 64;  // the generic kernel ignores tiles; any value gives a valid plan
 }
 
+extern "C" int b200attn_extend_block_q2(int32_t dqk, int32_t dv, int32_t group, int32_t q_dtype, int32_t kv_dtype,
+                                        int32_t kernel, int64_t num_q_tokens, int32_t batch_size) {
+  if (kernel != B200_KERNEL_GENERIC && b200::extend_fast_supported(dqk, dv, group, q_dtype, kv_dtype)) {
+    if (b200::extend_pair_supported(dqk, q_dtype, kv_dtype) && batch_size > 0 &&
+        num_q_tokens > (int64_t)batch_size * b200::extend_fast_block_q(group))
+      return b200::extend_pair_block_q(group);
+    return b200::extend_fast_block_q(group);
+  }
+  return 64;
+}
+
 extern "C" int b200attn_extend(const b200_extend_args* a, b200_stream_t stream_) {
   using namespace b200;
   B200_CHECK_ARG(a != nullptr, "extend: null args");

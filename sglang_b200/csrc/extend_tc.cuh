@@ -188,6 +188,7 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
     }
   } else {
     setmaxnreg_inc<kRegsSoftmax>();
+    auto signal_p_ready = [&](int t_) { mbar_arrive(bar(kBarPFull + t_)); };
 #include "extend_tc_softmax.inc"
   }
 
@@ -198,6 +199,8 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
     tmem_dealloc<kTmemCols>(tmem_base);
   }
 }
+
+#include "extend_tc_pair.cuh"
 
 bool extend_fast_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype) {
   if (dqk != dv || (dqk != 128 && dqk != 64)) return false;
@@ -292,7 +295,9 @@ template <typename QT, bool kFp8, int kHD>
 int launch_extend_fast_d(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr || p.custom_mask != nullptr;
   if constexpr (!kFp8) {
-    if (extend_tma_ok(p, a))
+    // tile::gather4 fills measured 2.3x SLOWER than LDGSTS at 128-byte rows (profiles/r2_extend_tma_gather4.md): the
+    // TMA path is taken only where it moves whole pages
+    if (a.page_size >= 16 && extend_tma_ok(p, a))
       return opts ? launch_extend_fast_t<QT, false, true, kHD, true>(p, a, stream)
                   : launch_extend_fast_t<QT, false, false, kHD, true>(p, a, stream);
   }
@@ -306,8 +311,20 @@ int launch_extend_fast_q(const ExtendParams& p, const b200_extend_args& a, cudaS
                              : launch_extend_fast_d<QT, kFp8, 128>(p, a, stream);
 }
 
+bool extend_pair_supported(int dqk, int q_dtype, int kv_dtype) { return dqk == 128 && kv_dtype == q_dtype; }
+
 int launch_extend_fast(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   const bool fp8 = a.kv_dtype == B200_FP8_E4M3 || a.kv_dtype == B200_FP8_E5M2;
+  const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr || p.custom_mask != nullptr;
+  const int bq1 = extend_fast_block_q(p.group), bq2 = extend_pair_block_q(p.group);
+  const int bq = a.block_q > 0 ? a.block_q : bq1;
+  if (bq == bq2 && extend_pair_supported(a.head_dim_qk, a.q_dtype, a.kv_dtype)) {
+    if (a.q_dtype == B200_BF16)
+      return opts ? launch_extend_pair_t<__nv_bfloat16, true>(p, a, stream)
+                  : launch_extend_pair_t<__nv_bfloat16, false>(p, a, stream);
+    return opts ? launch_extend_pair_t<__half, true>(p, a, stream) : launch_extend_pair_t<__half, false>(p, a, stream);
+  }
+  B200_CHECK_ARG(bq == bq1, "extend: plan block_q %d matches neither tcgen05 kernel (%d, %d)", bq, bq1, bq2);
   if (a.q_dtype == B200_BF16)
     return fp8 ? launch_extend_fast_q<__nv_bfloat16, true>(p, a, stream)
                : launch_extend_fast_q<__nv_bfloat16, false>(p, a, stream);

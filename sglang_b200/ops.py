@@ -351,6 +351,7 @@ class ExtendWorkspace:
     max_tiles: int
     num_ctas: int
     plan: torch.Tensor
+    block_q: int = 0          # what the current plan was built with (set by extend_plan)
 
     @staticmethod
     def create(max_bs: int, max_tiles: int, device, *, num_ctas: int) -> "ExtendWorkspace":
@@ -360,7 +361,13 @@ class ExtendWorkspace:
 
 
 def extend_block_q(head_dim_qk: int, head_dim_v: int, group: int, q_dtype, kv_dtype,
-                   kernel: int = KERNEL_AUTO) -> int:
+                   kernel: int = KERNEL_AUTO, num_tokens: int = 0, batch_size: int = 0) -> int:
+    """Query tokens per work item of the kernel that will run.  With the forward's size (`num_tokens` new tokens over
+    `batch_size` requests) long extends are planned for the CTA-pair kernel, whose items are twice as large; pass the
+    result to `extend_plan` (it is remembered in the workspace and handed to the launch)."""
+    if num_tokens > 0 and batch_size > 0:
+        return int(_C.lib.b200attn_extend_block_q2(head_dim_qk, head_dim_v, group, dtype_code(q_dtype),
+                                                   dtype_code(kv_dtype), kernel, num_tokens, batch_size))
     return int(_C.lib.b200attn_extend_block_q(head_dim_qk, head_dim_v, group, dtype_code(q_dtype),
                                               dtype_code(kv_dtype), kernel))
 
@@ -379,6 +386,7 @@ def extend_plan(ws: ExtendWorkspace, extend_seq_lens: torch.Tensor, block_q: int
         plan=ws.plan.data_ptr(),
     )
     _C.check(_C.lib.b200attn_extend_plan(C.byref(a), _stream()), "extend_plan")
+    ws.block_q = int(block_q)
     launch_count += 1
 
 
@@ -406,8 +414,10 @@ def extend_attention(
     custom_mask: Optional[torch.Tensor] = None,
     mask_indptr: Optional[torch.Tensor] = None,
     mask_skip_prefix: bool = True,
+    page_size: int = 1,
 ) -> torch.Tensor:
-    """`window_keys` > 0: query at position x attends kv positions (x - window_keys, x].  `sinks`: float32 [Hq].
+    """`page_size`: KV page size of the pool (pages are page_size-aligned runs of consecutive slots).
+    `window_keys` > 0: query at position x attends kv positions (x - window_keys, x].  `sinks`: float32 [Hq].
     `custom_mask` (uint8 / bool, flat) + `mask_indptr` (int64 [bs + 1]): request r, query i, kv position x is
     visible iff custom_mask[mask_indptr[r] + i * (P_r + E_r) + x]; it replaces the causal rule on the new tokens
     and, unless `mask_skip_prefix`, also masks the prefix (reference extend_attention.py:378-390,525-539)."""
@@ -443,6 +453,7 @@ def extend_attention(
         pool_slots=k_cache.shape[0],
         window_keys=max(0, int(window_keys)), sinks=_f32_vec(sinks, Hq, "sinks"),
         mask_skip_prefix=1 if mask_skip_prefix else 0,
+        block_q=ws.block_q, page_size=max(1, int(page_size)),
     )
     if custom_mask is not None:
         if mask_indptr is None:

@@ -55,21 +55,35 @@ def make_extend_problem(Hq, Hkv, D, prefix, extend, page_size, dtype, pool_dtype
 
 
 def run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, kernel=0, causal=True, want_lse=False):
+    """Runs the kernel the planner would pick for a short forward (one-CTA tcgen05 / generic) and -- where the
+    CTA-pair kernel covers the shape (D = 128, 16-bit pool) -- the pair kernel too; both must agree, the pair
+    kernel's output is returned."""
     from sglang_b200 import ops
 
     sm, _, _ = ops.device_info()
     T, Hq, D = q.shape
     group = Hq // kp.shape[1]
-    bq = ops.extend_block_q(D, D, group, q.dtype, pool_dtype, kernel)
-    ws = ops.ExtendWorkspace.create(len(pre), T // bq + len(pre) + 1, "cuda", num_ctas=sm)
     ext_g, pre_g = ext.cuda(), pre.cuda()
-    ops.extend_plan(ws, ext_g, bq)
-    o = torch.empty_like(q, device="cuda")
-    lse = torch.empty(T, Hq, dtype=torch.float32, device="cuda") if want_lse else None
-    ops.extend_attention(q.cuda(), o, kp.cuda(), vp.cuda(), rtt.cuda(), rpi.cuda(), pre_g, ext_g, ws, scale,
-                         kv_dtype=pool_dtype, kernel=kernel, causal=causal, lse=lse)
-    torch.cuda.synchronize()
-    return o.float().cpu(), lse
+    qg, kg, vg, rg, ig = q.cuda(), kp.cuda(), vp.cuda(), rtt.cuda(), rpi.cuda()
+
+    def run(bq):
+        ws = ops.ExtendWorkspace.create(len(pre), T // bq + len(pre) + 1, "cuda", num_ctas=sm)
+        ops.extend_plan(ws, ext_g, bq)
+        o = torch.empty_like(q, device="cuda")
+        lse = torch.empty(T, Hq, dtype=torch.float32, device="cuda") if want_lse else None
+        ops.extend_attention(qg, o, kg, vg, rg, ig, pre_g, ext_g, ws, scale, kv_dtype=pool_dtype, kernel=kernel,
+                             causal=causal, lse=lse)
+        torch.cuda.synchronize()
+        return o.float().cpu(), lse
+
+    bq1 = ops.extend_block_q(D, D, group, q.dtype, pool_dtype, kernel)
+    bq2 = ops.extend_block_q(D, D, group, q.dtype, pool_dtype, kernel, num_tokens=1 << 30, batch_size=1)
+    o, lse = run(bq1)
+    if bq2 != bq1:
+        o2, lse2 = run(bq2)
+        assert float((o2 - o).abs().max()) <= 2e-3, "CTA-pair kernel disagrees with the one-CTA kernel"
+        return o2, lse2
+    return o, lse
 
 
 SHAPES = [
