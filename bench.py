@@ -333,9 +333,11 @@ def time_graph(graph, prep, steps, barrier):
     return a.elapsed_time(b) / steps
 
 
-def measure_extend(device, peaks):
+def measure_extend(device, peaks, page=1):
     """BASELINE configs[4] (cfg5): 128 requests sharing a 16K-token prefix, 1K-token extend each, Llama-8B heads;
-    one layer's extend attention, CUDA events, own clocks sample.  The second headline of `metric`."""
+    one layer's extend attention, CUDA events, own clocks sample.  The second headline of `metric`.
+    page 1 is the reference Triton backend's default pool (K/V rows gathered one by one with cp.async); page 64 is
+    the page-granular pool the reference's trtllm_mha / fa4 backends require (K/V pages fetched by TMA boxes)."""
     sys.path.insert(0, str(REPO / "benchmarks"))
     import sweep
 
@@ -344,7 +346,7 @@ def measure_extend(device, peaks):
     sampler.start()
     time.sleep(0.15)
     t0 = time.perf_counter()
-    r = sweep.extend_case("cfg5: 128 req x (16K shared prefix + 1K new)", bs, P, E, Hq, Hkv, D, 5)
+    r = sweep.extend_case("cfg5: 128 req x (16K shared prefix + 1K new)", bs, P, E, Hq, Hkv, D, 5, page=page)
     torch.cuda.synchronize()
     clocks = sampler.stop(t0, time.perf_counter())
     tf = r["tflops"]
@@ -352,8 +354,9 @@ def measure_extend(device, peaks):
     peak = float(sustained or 1413.7)
     return {
         "metric": "extend_attention_tflops", "value": tf, "unit": "TFLOP/s", "ms": r["ms"],
-        "config": {"workload": "llama-3.1-8b extend attention, 128 req x (16384 shared prefix + 1024 new), page_size 1 "
-                               "(BASELINE cfg5)", "layers": 1, "heads": [Hq, Hkv], "head_dim": D},
+        "config": {"workload": f"llama-3.1-8b extend attention, 128 req x (16384 shared prefix + 1024 new), page_size {page} "
+                               "(BASELINE cfg5)", "layers": 1, "heads": [Hq, Hkv], "head_dim": D,
+                   "kv_fill": "tma_page_boxes" if r.get("page_box_rows") else "cp_async_row_gather"},
         "flops": extend_flops(bs, P, E, Hq, D),
         "roofline": {"bound": "tensor", "kernel": "extend_tc_kernel<bf16, D128>", "achieved": tf, "peak": peak,
                      "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (a 30 ms kernel repeated back to back "
@@ -617,8 +620,10 @@ def run_ours(args):
         del st.qkv
         try:
             line["extend"] = measure_extend(device, peaks)
+            line["extend_page64"] = measure_extend(device, peaks, page=64)
         except Exception as e:  # noqa: BLE001
-            line["extend"] = {"error": f"{type(e).__name__}: {e}"}
+            line.setdefault("extend", {"error": f"{type(e).__name__}: {e}"})
+            line.setdefault("extend_page64", {"error": f"{type(e).__name__}: {e}"})
         line["secondary"] = secondary_measurements()
     if not args.no_cpu_baseline and world == 1:
         sample_bs = 8 if cfg["name"] == "cfg2" else 1

@@ -150,7 +150,7 @@ def extend_compare(name, bs, P, E, Hq, Hkv, D, iters=5):
     pre = torch.full((bs,), P, dtype=torch.int32, device=dev)
     ext = torch.full((bs,), E, dtype=torch.int32, device=dev)
     sm, _, _ = ops.device_info()
-    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, torch.bfloat16, 0, num_tokens=T, batch_size=bs)
+    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, torch.bfloat16, 0)
     ws = ops.ExtendWorkspace.create(bs, T // bq + bs + 1, dev, num_ctas=sm)
     ops.extend_plan(ws, ext, bq)
 
@@ -218,7 +218,7 @@ def _paged_extend_inputs(bs, P, E, Hq, Hkv, D, page):
     return q, kp, vp, rtt, pages
 
 
-def extend_compare_blackwell(name, bs, P, E, Hq, Hkv, D, page, iters=5):
+def extend_compare_blackwell(name, bs, P, E, Hq, Hkv, D, page, iters=5, ours_only=False):
     """Ours vs the shipped Blackwell kernels on the same page-granular pool: trtllm-gen context attention
     (flashinfer.prefill.trtllm_batch_context_with_kv_cache, trtllm_mha_backend.py:1315), the reference's vendored FA4
     (flash_attn/cute/interface.py flash_attn_varlen_func with page_table) and the reference's Triton extend kernel."""
@@ -232,16 +232,25 @@ def extend_compare_blackwell(name, bs, P, E, Hq, Hkv, D, page, iters=5):
     pre = torch.full((bs,), P, dtype=torch.int32, device=dev)
     ext = torch.full((bs,), E, dtype=torch.int32, device=dev)
     sm, _, _ = ops.device_info()
-    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, torch.bfloat16, 0, num_tokens=T, batch_size=bs)
+    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, torch.bfloat16, 0)
     ws = ops.ExtendWorkspace.create(bs, T // bq + bs + 1, dev, num_ctas=sm)
-    ops.extend_plan(ws, ext, bq)
+    ops.extend_plan(ws, ext, bq, page_size=page, req_to_token=rtt, req_pool_indices=rpi, extend_prefix_lens=pre)
 
-    def ours():
-        ops.extend_attention(q, o, kp, vp, rtt, rpi, pre, ext, ws, D**-0.5, kernel=0, kv_dtype=torch.bfloat16)
+    def ours(pg=page):
+        ops.extend_attention(q, o, kp, vp, rtt, rpi, pre, ext, ws, D**-0.5, kernel=0, kv_dtype=torch.bfloat16,
+                             page_size=pg)
 
+    # what the backend runs at this page size (TMA page boxes for page >= 16, LDGSTS row gather for page 1) ...
     t = time_cuda(ours, iters, warmup=2)
-    out["b200attn"] = dict(ms=round(t * 1e3, 3), TFLOPs=round(flops / t / 1e12, 1))
+    out["b200attn"] = dict(ms=round(t * 1e3, 3), TFLOPs=round(flops / t / 1e12, 1),
+                           fill="tma_page_boxes" if page >= 16 else "ldgsts_row_gather")
     o_ours = o.clone()
+    if page >= 16:  # ... and the row gather on the same pool, for the A/B
+        t1 = time_cuda(lambda: ours(1), iters, warmup=2)
+        out["b200attn_row_gather"] = dict(ms=round(t1 * 1e3, 3), TFLOPs=round(flops / t1 / 1e12, 1),
+                                          max_abs_vs_page_fill=round(float((o.float() - o_ours.float()).abs().max()), 6))
+    if ours_only:
+        return out
     cu_q = torch.arange(0, bs + 1, device=dev, dtype=torch.int32) * E
     cu_k = torch.arange(0, bs + 1, device=dev, dtype=torch.int32) * (P + E)
     seq_k = torch.full((bs,), P + E, dtype=torch.int32, device=dev)
@@ -376,13 +385,15 @@ def main():
         emit(decode_compare("cfg4 70B tp8 bs32 ctx32768 page1", 32, 32768, 8, 1, 128, 1, False))
     if args.only in (None, "extend"):
         emit(extend_compare("cfg5/16 8 req x (16K shared prefix + 1K)", 8, 16384, 1024, 32, 8, 128))
-    if args.only in (None, "blackwell"):
+    if args.only in (None, "blackwell", "ours"):
+        oo = args.only == "ours"
         for page in (1, 16, 64, 128):
             emit(extend_compare_blackwell(f"cfg5/16 8 req x (16K shared prefix + 1K), page {page}", 8, 16384, 1024,
-                                          32, 8, 128, page))
-        emit(extend_compare_blackwell("prefill 8 req x 4K no prefix, page 64", 8, 0, 4096, 32, 8, 128, 64))
+                                          32, 8, 128, page, ours_only=oo))
+        emit(extend_compare_blackwell("prefill 8 req x 4K no prefix, page 64", 8, 0, 4096, 32, 8, 128, 64,
+                                      ours_only=oo))
         emit(extend_compare_blackwell("cfg5 128 req x (16K shared prefix + 1K), page 64", 128, 16384, 1024, 32, 8,
-                                      128, 64, iters=3))
+                                      128, 64, iters=3, ours_only=oo))
     if args.only in (None, "triton"):
         emit(decode_compare_triton("cfg2 8B bf16 bs64 ctx4096 page1", 64, 4096, 32, 8, 128))
         emit(decode_compare_triton("cfg4 70B tp8 bs32 ctx32768 page1", 32, 32768, 8, 1, 128))

@@ -96,15 +96,23 @@ def decode_case(name, bs, L, Hq, Hkv, D, pool_dtype, page, iters, ragged=False):
                 us_eager=round(t_eager * 1e6, 1))
 
 
-def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_dtype=torch.bfloat16, tree_mask=False):
+def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_dtype=torch.bfloat16, tree_mask=False,
+                page=1):
+    """`page` > 1: the pool is page-granular (random page order, slots consecutive inside a page -- what SGLang's
+    paged allocator hands out); P and E must be multiples of it."""
     dev = "cuda"
     g = torch.Generator(device=dev).manual_seed(0)
-    rows = (P if shared else bs * P) + bs * E + 1
+    assert P % page == 0 and E % page == 0
+    rows = (P if shared else bs * P) + bs * E + page
     kp = torch.randn(rows, Hkv, D, generator=g, device=dev, dtype=torch.bfloat16)
     vp = torch.randn(rows, Hkv, D, generator=g, device=dev, dtype=torch.bfloat16)
     if pool_dtype in (torch.float8_e4m3fn, torch.float8_e5m2):
         kp, vp = kp.to(pool_dtype).view(torch.uint8), vp.to(pool_dtype).view(torch.uint8)
-    perm = torch.randperm(rows - 1, generator=g, device=dev).int() + 1
+    if page == 1:
+        perm = torch.randperm(rows - 1, generator=g, device=dev).int() + 1
+    else:
+        pages = torch.randperm(rows // page - 1, generator=g, device=dev).int() + 1
+        perm = (pages.view(-1, 1) * page + torch.arange(page, device=dev, dtype=torch.int32).view(1, -1)).reshape(-1)
     rtt = torch.zeros(bs + 1, P + E, dtype=torch.int32, device=dev)
     if shared:
         rtt[1:, :P] = perm[:P]
@@ -118,9 +126,9 @@ def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_d
     pre = torch.full((bs,), P, dtype=torch.int32, device=dev)
     ext = torch.full((bs,), E, dtype=torch.int32, device=dev)
     sm, _, _ = ops.device_info()
-    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, pool_dtype, kernel, num_tokens=T, batch_size=bs)
+    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, pool_dtype, kernel)
     ws = ops.ExtendWorkspace.create(bs, T // bq + bs + 1, dev, num_ctas=sm)
-    ops.extend_plan(ws, ext, bq)
+    ops.extend_plan(ws, ext, bq, page_size=page, req_to_token=rtt, req_pool_indices=rpi, extend_prefix_lens=pre)
 
     mkw = {}
     if tree_mask:   # TARGET_VERIFY shape: a chain "tree" (lower-triangular) over the E draft tokens, prefix unmasked
@@ -130,13 +138,14 @@ def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_d
                    mask_indptr=torch.arange(bs + 1, device=dev, dtype=torch.int64) * (E * (P + E)))
 
     def fn():
-        ops.extend_attention(q, o, kp, vp, rtt, rpi, pre, ext, ws, D**-0.5, kernel=kernel, kv_dtype=pool_dtype, **mkw)
+        ops.extend_attention(q, o, kp, vp, rtt, rpi, pre, ext, ws, D**-0.5, kernel=kernel, kv_dtype=pool_dtype,
+                             page_size=page, **mkw)
 
     t = time_cuda(fn, iters, warmup=2)
     flops = 4 * Hq * D * bs * (E * P + E * (E + 1) / 2)
     tf = flops / t / 1e12
     return dict(case=name, kind="extend", ms=round(t * 1e3, 3), tflops=round(tf, 1), frac_measured=round(tf / TF, 3),
-                frac_nominal=round(tf / 2250, 3))
+                frac_nominal=round(tf / 2250, 3), page_size=page, page_box_rows=int(ws.plan[4]))
 
 
 def store_case(name, T, Hkv, D, pool_dtype, iters):

@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 4
+#define B200ATTN_ABI_VERSION 5
 
 typedef void* b200_stream_t; /* a cudaStream_t */
 
@@ -204,6 +204,16 @@ typedef struct b200_extend_plan_args {
   int32_t max_tiles;
   int32_t block_q;              /* query rows (tokens) per tile */
   int32_t* plan;
+  /* Optional page check (req_to_token != NULL and page_size a power of two >= 16): the plan also verifies, on the
+   * device, that every request's positions sit on consecutive pool rows inside each page, which lets
+   * b200attn_extend(page_size) fetch K/V by TMA page boxes.  A table that fails (or no check) is read row by row --
+   * the result is the same either way. */
+  const int32_t* req_to_token;
+  int64_t req_to_token_stride;
+  const void* req_pool_indices;     /* [bs] */
+  int32_t req_pool_indices_is_i64;
+  const void* extend_prefix_lens;   /* [bs], same integer type as extend_seq_lens */
+  int32_t page_size;
 } b200_extend_plan_args;
 
 int b200attn_extend_plan(const b200_extend_plan_args* args, b200_stream_t stream);
@@ -252,8 +262,8 @@ typedef struct b200_extend_args {
                                    != 0.  Replaces the causal rule on the new tokens (x >= P_r); NULL = none */
   const int64_t* mask_indptr;   /* [bs + 1] offsets into custom_mask */
   int32_t mask_skip_prefix;     /* 1: prefix positions (x < P_r) are always visible (SKIP_PREFIX_CUSTOM_MASK) */
-  int32_t block_q;              /* the block_q the plan was built with (b200attn_extend_block_q2): selects the
-                                   one-CTA or the CTA-pair tcgen05 kernel; 0 = the one-CTA value */
+  int32_t block_q;              /* the block_q the plan was built with (checked against the kernel's tile size;
+                                   0 = not stated) */
   int32_t page_size;            /* KV page size of the pool (req_to_token entries of one page are consecutive slots,
                                    pages are page_size-aligned); >= 16 lets the fill use one TMA box per page; 0/1 =
                                    token-granular */
@@ -265,11 +275,6 @@ int b200attn_extend_fast_supported(int32_t head_dim_qk, int32_t head_dim_v, int3
 /* query tokens per tile the kernel that would be picked uses (for the plan) */
 int b200attn_extend_block_q(int32_t head_dim_qk, int32_t head_dim_v, int32_t group,
                             int32_t q_dtype, int32_t kv_dtype, int32_t kernel);
-/* the same, given the host-known size of the forward (sum E_r, batch size): requests that extend by more than one
- * CTA's worth of query tokens on average are planned for the CTA-pair kernel (D = 128, 16-bit pool), whose work
- * items are twice as large.  Pass the result to b200attn_extend_plan and in b200_extend_args.block_q. */
-int b200attn_extend_block_q2(int32_t head_dim_qk, int32_t head_dim_v, int32_t group, int32_t q_dtype,
-                             int32_t kv_dtype, int32_t kernel, int64_t num_q_tokens, int32_t batch_size);
 
 /* ------------------------------------------------------------------------ *
  * Fused rotary embedding + KV-store (the step right before RadixAttention.forward).

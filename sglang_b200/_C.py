@@ -14,7 +14,7 @@ LIB_PATH = Path(os.environ.get("B200ATTN_LIB", _PKG_DIR / "lib" / "libb200attn.s
 
 B200_BF16, B200_F16, B200_FP8_E4M3, B200_FP8_E5M2 = 0, 1, 2, 3
 KERNEL_AUTO, KERNEL_GENERIC, KERNEL_FAST = 0, 1, 2
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 i32, i64, f32, vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
@@ -76,6 +76,8 @@ class ExtendPlanArgs(C.Structure):
     _fields_ = [
         ("extend_seq_lens", vp), ("lens_is_i64", i32), ("batch_size", i32), ("max_bs", i32),
         ("max_tiles", i32), ("block_q", i32), ("plan", vp),
+        ("req_to_token", vp), ("req_to_token_stride", i64), ("req_pool_indices", vp),
+        ("req_pool_indices_is_i64", i32), ("extend_prefix_lens", vp), ("page_size", i32),
     ]
 
 
@@ -140,7 +142,6 @@ SYMBOLS = {
     "b200attn_extend": (C.c_int, [C.POINTER(ExtendArgs), vp]),
     "b200attn_extend_fast_supported": (C.c_int, [i32] * 5),
     "b200attn_extend_block_q": (C.c_int, [i32] * 6),
-    "b200attn_extend_block_q2": (C.c_int, [i32] * 6 + [i64, i32]),
     "b200attn_merge_state": (C.c_int, [C.POINTER(MergeStateArgs), vp]),
     "b200attn_oproj_allreduce": (C.c_int, [C.POINTER(OProjAllReduceArgs), vp]),
     "b200attn_oproj_allreduce_flag_words": (i64, [i32]),

@@ -138,11 +138,8 @@ class B200AttnBackend(_Base):
         self._ext_lens = None          # (prefix_lens, extend_lens, custom_mask, mask_indptr) of this forward
         self._graph_state_frozen = False
         group = self.num_head // self.num_kv_head
-        # smallest work item any extend kernel uses (sizes the work lists); the per-forward value is chosen in
-        # init_forward_metadata_out_graph from the forward's size
-        self._extend_min_block_q = ops.extend_block_q(self.head_dim, self.v_head_dim, group, self._q_dtype,
-                                                      self.kv_dtype, self.extend_kernel)
-        self._extend_block_q = self._extend_min_block_q
+        self._extend_block_q = ops.extend_block_q(self.head_dim, self.v_head_dim, group, self._q_dtype,
+                                                  self.kv_dtype, self.extend_kernel)
         self.num_draft_tokens = _spec_num_draft_tokens(model_runner)
         self.forward_metadata = None
         #: optional (start, stop) torch.cuda.Event pair re-recorded around the next decode attention kernel
@@ -179,7 +176,7 @@ class B200AttnBackend(_Base):
         a replay) gets the same set back, so the replay refills exactly the buffers the graph reads.  Sets that a
         graph holds are never reallocated or freed; other eager batches use the graph set when they
         fit it, else a separate eager set that grows geometrically."""
-        tiles = tokens // self._extend_min_block_q + bs + 1
+        tiles = tokens // self._extend_block_q + bs + 1
         st = self._ext_captured.get(key)
         if st is not None and st.fits(bs, tiles, mask_bytes):
             return st
@@ -256,7 +253,6 @@ class B200AttnBackend(_Base):
                 torch.cumsum((pre.to(torch.int64) + n) * n, dim=0, out=mask_indptr[1:])
                 mask = st.mask
             self._ext, self._ext_lens = st, (pre, ext, mask, mask_indptr)
-            self._pick_block_q(bs * n, bs)
         elif not eager_lens and mode.is_draft_extend_v2():
             # CUDA-graph draft-extend: a fixed number of query rows per request; the cached prefix is
             # seq_lens - accepted tokens, clamped for padded rows (triton_backend.py:529-565)
@@ -274,19 +270,12 @@ class B200AttnBackend(_Base):
             else:
                 pre.copy_(seq)
             self._ext, self._ext_lens = st, (pre, ext, None, None)
-            self._pick_block_q(bs * n, bs)
         else:
             T = getattr(forward_batch, "extend_num_tokens", None)
             if T is None:
                 T = forward_batch.out_cache_loc.shape[0]
             self._ext = self._select_ext((int(mode), bs), bs, int(T), 0, in_capture)
             self._ext_lens = (forward_batch.extend_prefix_lens, forward_batch.extend_seq_lens, None, None)
-            self._pick_block_q(int(T), bs)
-
-    def _pick_block_q(self, tokens: int, bs: int) -> None:
-        self._extend_block_q = ops.extend_block_q(self.head_dim, self.v_head_dim, self.num_head // self.num_kv_head,
-                                                  self._q_dtype, self.kv_dtype, self.extend_kernel,
-                                                  num_tokens=int(tokens), batch_size=int(bs))
 
     def init_forward_metadata_in_graph(self, forward_batch):
         """One planner launch (static shape, graph-recordable, no host sync, reads persistent buffers only)."""
@@ -301,7 +290,15 @@ class B200AttnBackend(_Base):
                 ops.decode_plan(self.decode_ws_swa, seq_lens, self.num_kv_head, waves=self.DECODE_WAVES,
                                 items_per_chunk=self._decode_items, window_keys=self.sliding_window_size + 1)
         else:
-            ops.extend_plan(self._ext.ws, self._ext_lens[1], self._extend_block_q)
+            pre, ext = self._ext_lens[0], self._ext_lens[1]
+            # page_size >= 16: the plan also verifies that pages are runs of consecutive pool rows (the paged
+            # allocator's layout), which lets forward_extend fetch K/V by TMA page boxes
+            paged = self.page_size >= 16 and pre is not None and pre.dtype == ext.dtype
+            ops.extend_plan(self._ext.ws, ext, self._extend_block_q,
+                            page_size=self.page_size if paged else 1,
+                            req_to_token=self.req_to_token_pool.req_to_token if paged else None,
+                            req_pool_indices=forward_batch.req_pool_indices[: ext.shape[0]] if paged else None,
+                            extend_prefix_lens=pre if paged else None)
 
     # ------------------------------------------------------------------ CUDA graphs
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
@@ -319,7 +316,7 @@ class B200AttnBackend(_Base):
                 waves=self.DECODE_WAVES)
             self.decode_ws_swa = self._swa_workspace(self.decode_ws)
         g = self._ext_graph
-        tiles = max_num_tokens // self._extend_min_block_q + max_bs + 1
+        tiles = max_num_tokens // self._extend_block_q + max_bs + 1
         # custom (tree) masks of TARGET_VERIFY: draft tokens x (context + draft tokens) bytes per request, the
         # reference's bound (triton_backend.py:1013-1017)
         mask_bytes = max_num_tokens * self.max_context_len if self.num_draft_tokens > 0 else 0

@@ -185,5 +185,6 @@ constexpr float kLn2 = 0.6931471805599453f;
 
 // plan buffer layout shared by the planner kernels and their consumers
 constexpr int kPlanHeader = 8;
+constexpr int kPlanPageRows = 4;   // extend plan: rows per verified page box (0 = page table not verified)
 
 }  // namespace b200

@@ -30,6 +30,13 @@ struct ExtPlanParams {
   const void* extend_seq_lens;
   int32_t* plan;
   int32_t lens_is_i64, batch_size, max_bs, max_tiles, block_q;
+  int32_t page_rows;            // rows per page box to verify (0: no page check, plan[kPlanPageRows] = 0)
+  // page check only
+  const void* extend_prefix_lens;
+  const int32_t* req_to_token;
+  int64_t req_to_token_stride;
+  const void* req_pool_indices;
+  int32_t req_pool_indices_is_i64;
 };
 
 constexpr int kPlanThreads = 1024;
@@ -95,7 +102,31 @@ __global__ void __launch_bounds__(kPlanThreads) extend_plan_kernel(const ExtPlan
     p.plan[1] = p.block_q;
     p.plan[2] = bs;
     p.plan[3] = s_carry_q;
+    p.plan[kPlanPageRows] = p.page_rows;   // cleared by extend_page_check_kernel when a box would not be contiguous
   }
+}
+
+// Page check: the TMA fill of the tcgen05 kernel reads positions [b * R, (b + 1) * R) of a request as ONE box of R
+// consecutive pool rows starting at the slot of position b * R.  SGLang's paged allocator guarantees that for
+// R | page_size, but req_to_token itself is token-granular and the reference's kernels never assume more (its own
+// unit-test kit scatters the new tokens of a request inside their page, dense_attention.py:685-703), so the
+// plan verifies it per batch: grid (chunks, bs), one comparison per position, any mismatch clears the flag.
+constexpr int kPageCheckThreads = 256, kPageCheckChunks = 8;
+
+__global__ void __launch_bounds__(kPageCheckThreads) extend_page_check_kernel(const ExtPlanParams p) {
+  bool bad = false;
+  for (int r = blockIdx.y; r < p.batch_size; r += gridDim.y) {
+  const int64_t E = load_index(p.extend_seq_lens, p.lens_is_i64, r);
+  const int64_t P = load_index(p.extend_prefix_lens, p.lens_is_i64, r);
+  const int L = (int)((P > 0 ? P : 0) + (E > 0 ? E : 0));
+  const int32_t* pt = p.req_to_token + load_index(p.req_pool_indices, p.req_pool_indices_is_i64, r) * p.req_to_token_stride;
+  const int R = p.page_rows;
+  for (int pos = blockIdx.x * kPageCheckThreads + threadIdx.x; pos < L; pos += kPageCheckChunks * kPageCheckThreads) {
+    const int in_box = pos & (R - 1);
+    bad |= __ldg(pt + pos) != __ldg(pt + pos - in_box) + in_box;
+  }
+  }
+  if (__syncthreads_or(bad) && threadIdx.x == 0) p.plan[kPlanPageRows] = 0;
 }
 
 struct ExtendParams {
@@ -120,7 +151,8 @@ struct ExtendParams {
   int32_t window_keys;          // query at position x attends (x - window_keys, x]; 0 = off
   int32_t mask_skip_prefix;
   int32_t kv_e5m2;              // FP8 pool bytes are e5m2 (else e4m3); read by the tcgen05 kernel's FP8 producers only
-  int32_t pool_slots;           // rows of the pool buffers (TMA: a row index >= pool_slots is zero-filled)
+  int32_t pool_slots;           // rows of the pool buffers (TMA: a box at row >= pool_slots is zero-filled)
+  int32_t tma_rows;             // rows per TMA box (min(page_size, 128)); 0 when the fill is LDGSTS
   float sm_scale, k_scale, v_scale, logit_cap;
   const float* sinks;           // [Hq] natural-log sink logits or nullptr
   const uint8_t* custom_mask;   // see b200_extend_args
@@ -220,8 +252,20 @@ extern "C" int b200attn_extend_plan(const b200_extend_plan_args* a, b200_stream_
   ExtPlanParams p;
   p.extend_seq_lens = a->extend_seq_lens; p.plan = a->plan; p.lens_is_i64 = a->lens_is_i64;
   p.batch_size = a->batch_size; p.max_bs = a->max_bs; p.max_tiles = a->max_tiles; p.block_q = a->block_q;
-  extend_plan_kernel<<<1, kPlanThreads, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(p);
+  p.page_rows = a->req_to_token != nullptr ? extend_tma_rows(a->page_size) : 0;
+  p.extend_prefix_lens = a->extend_prefix_lens; p.req_to_token = a->req_to_token;
+  p.req_to_token_stride = a->req_to_token_stride; p.req_pool_indices = a->req_pool_indices;
+  p.req_pool_indices_is_i64 = a->req_pool_indices_is_i64;
+  B200_CHECK_ARG(p.page_rows == 0 || (a->extend_prefix_lens && a->req_pool_indices),
+                 "extend_plan: the page check needs extend_prefix_lens and req_pool_indices");
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  extend_plan_kernel<<<1, kPlanThreads, 0, stream>>>(p);
   B200_CHECK_CUDA(cudaGetLastError());
+  if (p.page_rows > 0 && a->batch_size > 0) {
+    extend_page_check_kernel<<<dim3(kPageCheckChunks, a->batch_size < 32768 ? a->batch_size : 32768), kPageCheckThreads, 0,
+                               stream>>>(p);
+    B200_CHECK_CUDA(cudaGetLastError());
+  }
   return B200_OK;
 }
 
@@ -235,17 +279,6 @@ extern "C" int b200attn_extend_block_q(int32_t dqk, int32_t dv, int32_t group, i
   if (kernel != B200_KERNEL_GENERIC && b200::extend_fast_supported(dqk, dv, group, q_dtype, kv_dtype))
     return b200::extend_fast_block_q(group);
   return 64;  // the generic kernel ignores tiles; any value gives a valid plan
-}
-
-extern "C" int b200attn_extend_block_q2(int32_t dqk, int32_t dv, int32_t group, int32_t q_dtype, int32_t kv_dtype,
-                                        int32_t kernel, int64_t num_q_tokens, int32_t batch_size) {
-  if (kernel != B200_KERNEL_GENERIC && b200::extend_fast_supported(dqk, dv, group, q_dtype, kv_dtype)) {
-    if (b200::extend_pair_supported(dqk, q_dtype, kv_dtype) && batch_size > 0 &&
-        num_q_tokens > (int64_t)batch_size * b200::extend_fast_block_q(group))
-      return b200::extend_pair_block_q(group);
-    return b200::extend_fast_block_q(group);
-  }
-  return 64;
 }
 
 extern "C" int b200attn_extend(const b200_extend_args* a, b200_stream_t stream_) {
@@ -282,6 +315,7 @@ extern "C" int b200attn_extend(const b200_extend_args* a, b200_stream_t stream_)
   p.window_keys = a->window_keys > 0 ? a->window_keys : 0; p.sinks = a->sinks;
   p.custom_mask = a->custom_mask; p.mask_indptr = a->mask_indptr; p.mask_skip_prefix = a->mask_skip_prefix;
   p.kv_e5m2 = a->kv_dtype == B200_FP8_E5M2;
+  p.tma_rows = 0;
   p.pool_slots = a->pool_slots > 0 && a->pool_slots < 0x7fffffff ? (int32_t)a->pool_slots : 0;
   B200_CHECK_ARG(a->custom_mask == nullptr || a->mask_indptr != nullptr, "extend: custom_mask needs mask_indptr");
   B200_CHECK_ARG(!(p.window_keys > 0 && !a->causal), "extend: a sliding window needs causal attention");

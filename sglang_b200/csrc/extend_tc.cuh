@@ -18,11 +18,14 @@
 //   warp  8      TMEM allocation + MMA issue (warp-uniform control flow, one elected lane issues)
 //   warps 9-11   idle (they only give their registers away)
 //   warps 12-15  producers.  Q once, with 16-byte cp.async into 128B-swizzled tiles.  K/V ring:
-//                * 16-bit pools (kTma): ONE warp issues TMA `cp.async.bulk.tensor.2d.tile::gather4` -- four
-//                  page-table rows per instruction, hardware 128B swizzle, completion counted in bytes on the
-//                  slot's mbarrier; 128 instructions fill a K + V block pair, no generic-proxy fence needed
-//                * FP8 pools / strided pools: page-table gather with cp.async by all four warps (FP8 bytes are
-//                  widened to f16 on the way), completion by cp.async.mbarrier.arrive
+//                * 16-bit pools with page_size >= 16 (kTma): ONE warp issues TMA `cp.async.bulk.tensor.2d` -- a
+//                  page's one-head slice is a strided box [page rows x 64 words] of the pool, landed with the
+//                  hardware 128B swizzle, completion counted in bytes on the slot's mbarrier (no generic-proxy
+//                  fence, no LDGSTS issue slots)
+//                * page_size 1 (SGLang's default), FP8 pools, strided pools: page-table gather with 16-byte cp.async
+//                  by all four warps (FP8 bytes are widened to f16 on the way), completion by
+//                  cp.async.mbarrier.arrive.  (tile::gather4 was measured 2.35x slower than LDGSTS at 128-byte
+//                  rows, profiles/r2_extend_experiments.md.)
 //
 // TMEM (512 columns): S0 [0,128)  S1 [128,256)  O0 [256,384)  O1 [384,512);  P_t = S_t columns [0,64).
 // Shared memory: Q0,Q1 32 KiB each | ring of 5 x 32 KiB slots filled K0 V0 K1 V1 ... | barriers.
@@ -106,7 +109,8 @@ __device__ __forceinline__ uint32_t swz_off(int row, int chunk, int rows) {
 // never touches the second 64-wide d half: the producers fill 128-byte rows, QK runs 4 k-steps instead of 8, PV is
 // an M128 x N64 MMA into 64 O columns.  (Its softmax cost per kv block is the same as for D = 128, so it is
 // exp-bound rather than MMA-bound.)
-// kTma: the K/V ring is filled by TMA gather4 through the two tensor maps (16-bit pools with contiguous heads).
+// kTma: the K/V ring may be filled by TMA page boxes through the two tensor maps (16-bit pools, page_size >= 16);
+// the instance also carries the row-gather producer and picks per launch from the plan's page check.
 template <typename QT, int kEmu, bool kFp8, bool kOpts, int kHD, bool kTma>
 __global__ void __launch_bounds__(tc::kThreads, 1)
 extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constant__ CUtensorMap tm_k,
@@ -150,12 +154,15 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
       (kOpts && p.window_keys > 0 && P + q_start + 1 > p.window_keys) ? P + q_start + 1 - p.window_keys : 0;
   const int kv_off = kv_first / kBlockKV * kBlockKV;
   const int n_blocks = (kv_end - kv_off + kBlockKV - 1) / kBlockKV;
+  // TMA page boxes only when the plan has verified that every box-sized run of positions of every request sits on
+  // consecutive pool rows (b200attn_extend_plan); any other page table is read row by row
+  const bool use_tma = kTma && p.plan[kPlanPageRows] == p.tma_rows;
 
   // ---- one-time setup --------------------------------------------------------------------------
   if (threadIdx.x == 0) {
     mbar_init(bar(kBarQFull), kProducerThreads);
     for (int s = 0; s < kSlots; ++s) {
-      mbar_init(bar(kBarFull + s), kTma ? 1 : kProducerThreads);
+      mbar_init(bar(kBarFull + s), use_tma ? 1 : kProducerThreads);
       mbar_init(bar(kBarEmpty + s), 1);
     }
     for (int t = 0; t < kQTiles; ++t) {
@@ -176,8 +183,10 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
     setmaxnreg_dec<kRegsOther>();
     if constexpr (kFp8) {
 #include "extend_tc_producer_fp8.inc"
-    } else if constexpr (kTma) {
+    } else if (use_tma) {
+      if constexpr (kTma) {
 #include "extend_tc_producer_tma.inc"
+      }
     } else {
 #include "extend_tc_producer.inc"
     }
@@ -188,7 +197,6 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
     }
   } else {
     setmaxnreg_inc<kRegsSoftmax>();
-    auto signal_p_ready = [&](int t_) { mbar_arrive(bar(kBarPFull + t_)); };
 #include "extend_tc_softmax.inc"
   }
 
@@ -200,7 +208,6 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
   }
 }
 
-#include "extend_tc_pair.cuh"
 
 bool extend_fast_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype) {
   if (dqk != dv || (dqk != 128 && dqk != 64)) return false;
@@ -223,8 +230,8 @@ bool extend_fast_layout_ok(const ExtendParams& p, int kv_dtype) {
 }
 
 // ---- TMA descriptors (host) -------------------------------------------------------------------------------------
-// The pool buffer [slots, Hkv * D] as a 2-D tensor of 16-bit words; box = 64 words x 1 row, SWIZZLE_128B: a gather4
-// lands four 128-byte rows exactly where the UMMA descriptors of this kernel expect them.  cuTensorMapEncodeTiled is
+// The pool buffer [slots, Hkv * D] as a 2-D tensor of 16-bit words; box = 64 words x `box_rows` rows, SWIZZLE_128B:
+// one copy lands the 128-byte rows of a page's one-head d half exactly where the UMMA descriptors expect them.  cuTensorMapEncodeTiled is
 // resolved through the runtime (no link-time dependency on libcuda).
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -244,27 +251,36 @@ EncodeTiledFn tensor_map_encoder() {
 }
 
 // rows x width 16-bit words, row pitch `stride_elems` words
-bool make_pool_tensor_map(CUtensorMap* tm, const void* base, int64_t rows, int64_t width, int64_t stride_elems) {
+bool make_pool_tensor_map(CUtensorMap* tm, const void* base, int64_t rows, int64_t width, int64_t stride_elems,
+                          int box_rows) {
   EncodeTiledFn enc = tensor_map_encoder();
   if (enc == nullptr) return false;
   const cuuint64_t gdim[2] = {(cuuint64_t)width, (cuuint64_t)rows};
   const cuuint64_t gstride[1] = {(cuuint64_t)stride_elems * 2};
-  const cuuint32_t box[2] = {64, 1};
+  const cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1, 1};
   return enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-// TMA needs: heads contiguous inside a pool row, 16-byte aligned base and row pitch, row ids that fit int32
+// rows per TMA box: the page (power of two >= 16), at most one 128-row kv block
+int extend_tma_rows(int page_size) {
+  if (page_size < 16 || (page_size & (page_size - 1)) != 0) return 0;
+  return page_size < tc::kBlockKV ? page_size : tc::kBlockKV;
+}
+
+// TMA needs: whole pages, heads contiguous inside a pool row, 16-byte aligned base and row pitch, int32 row ids
 bool extend_tma_ok(const ExtendParams& p, const b200_extend_args& a) {
-  return p.k_stride_h == p.head_dim_qk && p.v_stride_h == p.head_dim_v && a.pool_slots > 0 &&
+  return extend_tma_rows(a.page_size) > 0 && p.k_stride_h == p.head_dim_qk && p.v_stride_h == p.head_dim_v && a.pool_slots > 0 &&
          a.pool_slots < 0x7fffffff && p.k_stride_s % 8 == 0 && p.v_stride_s % 8 == 0 &&
          p.k_stride_s >= (int64_t)p.num_kv_heads * p.head_dim_qk && p.v_stride_s >= (int64_t)p.num_kv_heads * p.head_dim_v;
 }
 
 template <typename QT, bool kFp8, bool kOpts, int kHD, bool kTma>
-int launch_extend_fast_t(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
+int launch_extend_fast_t(const ExtendParams& p_in, const b200_extend_args& a, cudaStream_t stream) {
+  ExtendParams p = p_in;
+  p.tma_rows = kTma ? extend_tma_rows(a.page_size) : 0;
   static std::atomic<uint64_t> configured{0};
   constexpr int kSmem = tc::Layout<kFp8>::kSmemBytes;
   auto kern = extend_tc_kernel<QT, tc::kEmuEighths, kFp8, kOpts, kHD, kTma>;
@@ -273,8 +289,10 @@ int launch_extend_fast_t(const ExtendParams& p, const b200_extend_args& a, cudaS
   memset(&tm_k, 0, sizeof(tm_k));
   memset(&tm_v, 0, sizeof(tm_v));
   if (kTma) {
-    const bool ok = make_pool_tensor_map(&tm_k, p.k_cache, a.pool_slots, (int64_t)p.num_kv_heads * kHD, p.k_stride_s) &&
-                    make_pool_tensor_map(&tm_v, p.v_cache, a.pool_slots, (int64_t)p.num_kv_heads * kHD, p.v_stride_s);
+    const int rows = extend_tma_rows(a.page_size);
+    const bool ok =
+        make_pool_tensor_map(&tm_k, p.k_cache, a.pool_slots, (int64_t)p.num_kv_heads * kHD, p.k_stride_s, rows) &&
+        make_pool_tensor_map(&tm_v, p.v_cache, a.pool_slots, (int64_t)p.num_kv_heads * kHD, p.v_stride_s, rows);
     if (!ok) {
       set_error("extend: cuTensorMapEncodeTiled failed for the KV pool (%lld slots)", (long long)a.pool_slots);
       return B200_ECUDA;
@@ -295,9 +313,7 @@ template <typename QT, bool kFp8, int kHD>
 int launch_extend_fast_d(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr || p.custom_mask != nullptr;
   if constexpr (!kFp8) {
-    // tile::gather4 fills measured 2.3x SLOWER than LDGSTS at 128-byte rows (profiles/r2_extend_tma_gather4.md): the
-    // TMA path is taken only where it moves whole pages
-    if (a.page_size >= 16 && extend_tma_ok(p, a))
+    if (extend_tma_ok(p, a))      // page_size >= 16: TMA page boxes; page_size 1 keeps the LDGSTS gather
       return opts ? launch_extend_fast_t<QT, false, true, kHD, true>(p, a, stream)
                   : launch_extend_fast_t<QT, false, false, kHD, true>(p, a, stream);
   }
@@ -311,20 +327,11 @@ int launch_extend_fast_q(const ExtendParams& p, const b200_extend_args& a, cudaS
                              : launch_extend_fast_d<QT, kFp8, 128>(p, a, stream);
 }
 
-bool extend_pair_supported(int dqk, int q_dtype, int kv_dtype) { return dqk == 128 && kv_dtype == q_dtype; }
-
 int launch_extend_fast(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   const bool fp8 = a.kv_dtype == B200_FP8_E4M3 || a.kv_dtype == B200_FP8_E5M2;
-  const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr || p.custom_mask != nullptr;
-  const int bq1 = extend_fast_block_q(p.group), bq2 = extend_pair_block_q(p.group);
+  const int bq1 = extend_fast_block_q(p.group);
   const int bq = a.block_q > 0 ? a.block_q : bq1;
-  if (bq == bq2 && extend_pair_supported(a.head_dim_qk, a.q_dtype, a.kv_dtype)) {
-    if (a.q_dtype == B200_BF16)
-      return opts ? launch_extend_pair_t<__nv_bfloat16, true>(p, a, stream)
-                  : launch_extend_pair_t<__nv_bfloat16, false>(p, a, stream);
-    return opts ? launch_extend_pair_t<__half, true>(p, a, stream) : launch_extend_pair_t<__half, false>(p, a, stream);
-  }
-  B200_CHECK_ARG(bq == bq1, "extend: plan block_q %d matches neither tcgen05 kernel (%d, %d)", bq, bq1, bq2);
+  B200_CHECK_ARG(bq == bq1, "extend: the plan was built with block_q %d, the tcgen05 kernel needs %d", bq, bq1);
   if (a.q_dtype == B200_BF16)
     return fp8 ? launch_extend_fast_q<__nv_bfloat16, true>(p, a, stream)
                : launch_extend_fast_q<__nv_bfloat16, false>(p, a, stream);

@@ -109,16 +109,13 @@ __device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-// tile::gather4 (sm_100): FOUR arbitrary rows r0..r3 of a 2-D tensor, box-width elements starting at column c0,
-// land as four consecutive box rows at `dst` (hardware 128B swizzle from the tensor map); a row index outside the
-// tensor is zero-filled.  Completion is counted in bytes on `bar`.  The page-table gather of a token-granular KV
-// pool costs one instruction per 4 tokens instead of one LDGSTS per 16 bytes.
-__device__ __forceinline__ void tma_gather4(uint32_t dst, const void* tmap, uint32_t bar, int c0, int r0, int r1,
-                                            int r2, int r3) {
+// One box of a 2-D tensor map (tile mode): box_rows x box_cols elements starting at (column c0, row r0) land at
+// `dst` with the map's swizzle; a box that lies outside the tensor is zero-filled.  Completion is counted in bytes
+// on `bar`.
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint32_t bar, int c0, int r0) {
   asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile::gather4.mbarrier::complete_tx::bytes"
-      " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
-      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(r0), "r"(r1), "r"(r2), "r"(r3)
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(r0)
       : "memory");
 }
 __device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {

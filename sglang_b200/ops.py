@@ -361,13 +361,8 @@ class ExtendWorkspace:
 
 
 def extend_block_q(head_dim_qk: int, head_dim_v: int, group: int, q_dtype, kv_dtype,
-                   kernel: int = KERNEL_AUTO, num_tokens: int = 0, batch_size: int = 0) -> int:
-    """Query tokens per work item of the kernel that will run.  With the forward's size (`num_tokens` new tokens over
-    `batch_size` requests) long extends are planned for the CTA-pair kernel, whose items are twice as large; pass the
-    result to `extend_plan` (it is remembered in the workspace and handed to the launch)."""
-    if num_tokens > 0 and batch_size > 0:
-        return int(_C.lib.b200attn_extend_block_q2(head_dim_qk, head_dim_v, group, dtype_code(q_dtype),
-                                                   dtype_code(kv_dtype), kernel, num_tokens, batch_size))
+                   kernel: int = KERNEL_AUTO) -> int:
+    """Query tokens per work item of the kernel that will run; pass it to `extend_plan`."""
     return int(_C.lib.b200attn_extend_block_q(head_dim_qk, head_dim_v, group, dtype_code(q_dtype),
                                               dtype_code(kv_dtype), kernel))
 
@@ -377,7 +372,13 @@ def extend_fast_supported(head_dim_qk: int, head_dim_v: int, group: int, q_dtype
                                                       dtype_code(kv_dtype)))
 
 
-def extend_plan(ws: ExtendWorkspace, extend_seq_lens: torch.Tensor, block_q: int) -> None:
+def extend_plan(ws: ExtendWorkspace, extend_seq_lens: torch.Tensor, block_q: int, *,
+                page_size: int = 1, req_to_token: Optional[torch.Tensor] = None,
+                req_pool_indices: Optional[torch.Tensor] = None,
+                extend_prefix_lens: Optional[torch.Tensor] = None) -> None:
+    """Tile list for `extend_attention`.  With `page_size` >= 16 and the page table given, the plan also verifies on
+    the device that every page is a run of consecutive pool rows; `extend_attention(page_size=...)` then moves K/V by
+    TMA page boxes, otherwise (or when the check fails) row by row -- same result either way."""
     global launch_count
     _need_cuda(extend_seq_lens, ws.plan)
     a = _C.ExtendPlanArgs(
@@ -385,9 +386,24 @@ def extend_plan(ws: ExtendWorkspace, extend_seq_lens: torch.Tensor, block_q: int
         batch_size=extend_seq_lens.shape[0], max_bs=ws.max_bs, max_tiles=ws.max_tiles, block_q=block_q,
         plan=ws.plan.data_ptr(),
     )
+    check = page_size >= 16 and req_to_token is not None and extend_seq_lens.shape[0] > 0
+    if check:
+        if req_pool_indices is None or extend_prefix_lens is None:
+            raise ValueError("extend_plan: the page check needs req_pool_indices and extend_prefix_lens")
+        _need_cuda(req_to_token, req_pool_indices, extend_prefix_lens)
+        if req_to_token.dtype != torch.int32 or req_to_token.stride(1) != 1:
+            raise ValueError("req_to_token must be int32 with contiguous rows")
+        if extend_prefix_lens.dtype != extend_seq_lens.dtype:
+            raise ValueError("extend_prefix_lens and extend_seq_lens must share a dtype")
+        a.req_to_token = req_to_token.data_ptr()
+        a.req_to_token_stride = req_to_token.stride(0)
+        a.req_pool_indices = req_pool_indices.data_ptr()
+        a.req_pool_indices_is_i64 = _index_kind(req_pool_indices, "req_pool_indices")
+        a.extend_prefix_lens = extend_prefix_lens.data_ptr()
+        a.page_size = int(page_size)
     _C.check(_C.lib.b200attn_extend_plan(C.byref(a), _stream()), "extend_plan")
     ws.block_q = int(block_q)
-    launch_count += 1
+    launch_count += 2 if check and (page_size & (page_size - 1)) == 0 else 1
 
 
 def extend_attention(

@@ -54,36 +54,26 @@ def make_extend_problem(Hq, Hkv, D, prefix, extend, page_size, dtype, pool_dtype
         torch.tensor(extend, dtype=torch.int32)
 
 
-def run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, kernel=0, causal=True, want_lse=False):
-    """Runs the kernel the planner would pick for a short forward (one-CTA tcgen05 / generic) and -- where the
-    CTA-pair kernel covers the shape (D = 128, 16-bit pool) -- the pair kernel too; both must agree, the pair
-    kernel's output is returned."""
+def run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, kernel=0, causal=True, want_lse=False,
+                   page_size=1):
     from sglang_b200 import ops
 
     sm, _, _ = ops.device_info()
     T, Hq, D = q.shape
     group = Hq // kp.shape[1]
+    bq = ops.extend_block_q(D, D, group, q.dtype, pool_dtype, kernel)
+    ws = ops.ExtendWorkspace.create(len(pre), T // bq + len(pre) + 1, "cuda", num_ctas=sm)
     ext_g, pre_g = ext.cuda(), pre.cuda()
-    qg, kg, vg, rg, ig = q.cuda(), kp.cuda(), vp.cuda(), rtt.cuda(), rpi.cuda()
-
-    def run(bq):
-        ws = ops.ExtendWorkspace.create(len(pre), T // bq + len(pre) + 1, "cuda", num_ctas=sm)
-        ops.extend_plan(ws, ext_g, bq)
-        o = torch.empty_like(q, device="cuda")
-        lse = torch.empty(T, Hq, dtype=torch.float32, device="cuda") if want_lse else None
-        ops.extend_attention(qg, o, kg, vg, rg, ig, pre_g, ext_g, ws, scale, kv_dtype=pool_dtype, kernel=kernel,
-                             causal=causal, lse=lse)
-        torch.cuda.synchronize()
-        return o.float().cpu(), lse
-
-    bq1 = ops.extend_block_q(D, D, group, q.dtype, pool_dtype, kernel)
-    bq2 = ops.extend_block_q(D, D, group, q.dtype, pool_dtype, kernel, num_tokens=1 << 30, batch_size=1)
-    o, lse = run(bq1)
-    if bq2 != bq1:
-        o2, lse2 = run(bq2)
-        assert float((o2 - o).abs().max()) <= 2e-3, "CTA-pair kernel disagrees with the one-CTA kernel"
-        return o2, lse2
-    return o, lse
+    rtt_g, rpi_g = rtt.cuda(), rpi.cuda()
+    ops.extend_plan(ws, ext_g, bq, page_size=page_size, req_to_token=rtt_g, req_pool_indices=rpi_g,
+                    extend_prefix_lens=pre_g)
+    o = torch.empty_like(q, device="cuda")
+    lse = torch.empty(T, Hq, dtype=torch.float32, device="cuda") if want_lse else None
+    ops.extend_attention(q.cuda(), o, kp.cuda(), vp.cuda(), rtt_g, rpi_g, pre_g, ext_g, ws, scale,
+                         kv_dtype=pool_dtype, kernel=kernel, causal=causal, lse=lse, page_size=page_size)
+    torch.cuda.synchronize()
+    run_ops_extend.page_rows = int(ws.plan[4])     # rows per verified page box, 0 = row gather
+    return o.float().cpu(), lse
 
 
 SHAPES = [
@@ -96,6 +86,12 @@ SHAPES = [
     (4, 4, 80, [10, 0], [33, 17], 1),                  # odd head dim -> generic
     (4, 4, 256, [33], [70], 32),
     (16, 1, 128, [100], [150], 1),                     # group 16
+    # page-granular pools: K/V arrive by TMA page boxes (16-bit pools) -- ragged tails inside the last page,
+    # requests shorter than one page, pages larger than a 128-row kv block
+    (32, 8, 128, [0, 130, 64], [257, 1, 128], 64),
+    (8, 1, 128, [1000, 3], [300, 5], 128),
+    (8, 2, 128, [100, 700], [513, 20], 256),
+    (8, 2, 64, [31, 500], [200, 77], 32),
 ]
 
 
@@ -107,8 +103,38 @@ def test_extend_vs_oracle(shape, dtype, pool_dtype, kernel):
     Hq, Hkv, D, prefix, extend, page = shape
     q, kp, vp, rtt, rpi, pre, ext = make_extend_problem(Hq, Hkv, D, prefix, extend, page, dtype, pool_dtype, seed=D)
     scale = D**-0.5
-    got, _ = run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, kernel=KERNELS[kernel])
+    got, _ = run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, kernel=KERNELS[kernel], page_size=page)
     want = ref.extend_ref(q, kp, vp, rtt, rpi, pre, ext, scale, kv_dtype=pool_dtype)
+    assert_close_scaled(got, want)
+
+
+@pytest.mark.parametrize("page", [16, 64, 256])
+def test_page_box_fill_is_bit_identical_to_row_gather(page):
+    """Same pool, same page table: the TMA page-box fill and the cp.async row gather feed the same bytes to the same
+    MMAs, so the outputs are bit-equal -- including with NaN-free garbage in the unused tail of each last page."""
+    q, kp, vp, rtt, rpi, pre, ext = make_extend_problem(32, 8, 128, [0, 777, 130], [300, 129, 1], page,
+                                                        torch.bfloat16, torch.bfloat16, seed=page)
+    scale = 128**-0.5
+    a, _ = run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, torch.bfloat16, page_size=page)
+    assert run_ops_extend.page_rows == min(page, 128)
+    b, _ = run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, torch.bfloat16, page_size=1)
+    assert run_ops_extend.page_rows == 0
+    assert torch.equal(a, b)
+
+
+def test_scattered_page_table_falls_back_to_row_gather():
+    """req_to_token is token-granular: the reference kit's non_monotonic_extend layout permutes the new tokens'
+    slots inside their pages (dense_attention.py:685-703).  The plan's page check must see that and the kernel
+    must read row by row -- one swapped pair in one request is enough."""
+    page = 16
+    q, kp, vp, rtt, rpi, pre, ext = make_extend_problem(8, 2, 128, [40, 0], [200, 90], page, torch.bfloat16,
+                                                        torch.bfloat16, seed=77)
+    rtt = rtt.clone()
+    rtt[2, [35, 36]] = rtt[2, [36, 35]]
+    scale = 128**-0.5
+    got, _ = run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, torch.bfloat16, page_size=page)
+    assert run_ops_extend.page_rows == 0
+    want = ref.extend_ref(q, kp, vp, rtt, rpi, pre, ext, scale)
     assert_close_scaled(got, want)
 
 

@@ -159,7 +159,7 @@ def test_cfg5_full_size_shared_prefix_extend():
     pre = torch.full((bs,), P, dtype=torch.int32, device=dev)
     ext = torch.full((bs,), E, dtype=torch.int32, device=dev)
     sm, _, _ = ops.device_info()
-    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, torch.bfloat16, num_tokens=bs * E, batch_size=bs)
+    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, torch.bfloat16)
     ws = ops.ExtendWorkspace.create(bs, bs * E // bq + bs + 1, dev, num_ctas=sm)
     ops.extend_plan(ws, ext, bq)
     ops.extend_attention(q, o, kp, vp, rtt, rpi, pre, ext, ws, D ** -0.5)
@@ -200,7 +200,7 @@ def test_layer_buffer_larger_than_4gib():
     pre = torch.full((bs,), P, dtype=torch.int32, device="cuda")
     ext = torch.full((bs,), E, dtype=torch.int32, device="cuda")
     sm, _, _ = ops.device_info()
-    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, torch.bfloat16, num_tokens=bs * E, batch_size=bs)
+    bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, torch.bfloat16)
     ws = ops.ExtendWorkspace.create(bs, bs * E // bq + bs + 1, "cuda", num_ctas=sm)
     ops.extend_plan(ws, ext, bq)
     ops.extend_attention(qe, oe, kp, vp, rtt, torch.arange(1, bs + 1, device="cuda"), pre, ext, ws, D ** -0.5)
