@@ -330,3 +330,10 @@ extern "C" int b200attn_extend(const b200_extend_args* a, b200_stream_t stream_)
   if (a->q_dtype == B200_BF16) return launch_generic<__nv_bfloat16>(p, a->kv_dtype, a->num_ctas, stream);
   return launch_generic<__half>(p, a->kv_dtype, a->num_ctas, stream);
 }
+
+#if defined(B200_DEV) && defined(B200_TRACE)
+// dev builds only: copy the traced CTA's clock stamps out (16 slots x 512 kv blocks)
+extern "C" int b200attn_dev_trace_read(long long* out) {
+  return (int)cudaMemcpyFromSymbol(out, b200::g_ext_trace, sizeof(long long) * 16 * 512);
+}
+#endif

@@ -42,13 +42,30 @@
 #define B200_ABLATE_EXP 0
 #endif
 
+// Timeline trace of one CTA (dev builds with -DB200_TRACE=<block index>): lane 0 of selected warps stamps clock64 at
+// each hand-off of every kv block; read back with b200attn_dev_trace_read (benchmarks/_ab/trace_extend.py).
+#if defined(B200_DEV) && defined(B200_TRACE)
+__device__ long long g_ext_trace[16 * 512];
+#define B200_TR(slot, j)                                                                     \
+  do {                                                                                       \
+    if (blockIdx.x == (B200_TRACE) && (threadIdx.x & 31) == 0 && (j) < 512) {                \
+      long long c_;                                                                          \
+      asm volatile("mov.u64 %0, %%clock64;" : "=l"(c_)::"memory");                           \
+      g_ext_trace[(slot) * 512 + (j)] = c_;                                                  \
+    }                                                                                        \
+  } while (0)
+#else
+#define B200_TR(slot, j)
+#endif
+
 namespace {
 namespace tc {
 
 constexpr int kD = 128;            // head dim the tiles are laid out for (kHD = 64 uses the first 64-wide half)
 constexpr int kBlockKV = 128;      // kv tokens per MMA block
 constexpr int kQTiles = 2;
-constexpr int kSoftmaxWarps = 4;                     // per query tile
+constexpr int kSplit = 2;                            // threads per MMA row in the softmax (columns split between them)
+constexpr int kSoftmaxWarps = 4 * kSplit;            // all of them work on every query tile
 constexpr int kMmaWarp = 8;
 constexpr int kProducerWarp0 = 12;
 constexpr int kProducerWarps = 4;
@@ -80,7 +97,9 @@ struct Layout {
   static constexpr int kSmemKV = kSmemQ + kQTiles * kQTileBytes;
   static constexpr int kSmemRaw = kSmemKV + kSlots * kSlotBytes;
   static constexpr int kSmemBar = kSmemRaw + kRawBufs * kRawBytes;
-  static constexpr int kSmemBytes = kSmemBar + 256 + 1024;    // barriers + slack for the 1024-byte alignment
+  static constexpr int kSmemXchg = kSmemBar + 256;             // row-max / row-sum exchange of the softmax threads
+  static constexpr int kXchgBytes = kQTiles * kSplit * 128 * 2;
+  static constexpr int kSmemBytes = kSmemXchg + kXchgBytes + 1024;   // + slack for the 1024-byte alignment
   // barrier slots (8 bytes each)
   static constexpr int kBarQFull = 0;
   static constexpr int kBarFull = 1;                     // kSlots
