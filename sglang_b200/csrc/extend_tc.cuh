@@ -44,9 +44,10 @@
 
 // Timeline trace of one CTA (dev builds with -DB200_TRACE=<block index>): lane 0 of selected warps stamps clock64 at
 // each hand-off of every kv block; read back with b200attn_dev_trace_read (benchmarks/_ab/trace_extend.py).
+// -DB200_TRACE_WARPS instead stamps every softmax warp's P hand-off (benchmarks/_ab/trace_warps.py).
 #if defined(B200_DEV) && defined(B200_TRACE)
 __device__ long long g_ext_trace[16 * 512];
-#define B200_TR(slot, j)                                                                     \
+#define B200_TR_CORE(slot, j)                                                                \
   do {                                                                                       \
     if (blockIdx.x == (B200_TRACE) && (threadIdx.x & 31) == 0 && (j) < 512) {                \
       long long c_;                                                                          \
@@ -54,8 +55,27 @@ __device__ long long g_ext_trace[16 * 512];
       g_ext_trace[(slot) * 512 + (j)] = c_;                                                  \
     }                                                                                        \
   } while (0)
+#if defined(B200_TRACE_WARPS)
+#define B200_TR2(slot, j) B200_TR_CORE(slot, j)
+#define B200_TR(slot, j)
+#else
+#define B200_TR(slot, j) B200_TR_CORE(slot, j)
+#define B200_TR2(slot, j)
+#endif
 #else
 #define B200_TR(slot, j)
+#define B200_TR2(slot, j)
+#endif
+
+// tuning switches of the softmax pass (defaults = the shipped choice; dev builds override them for A/B runs)
+#ifndef B200_SUM_LATE
+#define B200_SUM_LATE 1
+#endif
+#ifndef B200_EMU
+#define B200_EMU 4      // sixteenths of the column pairs that take the polynomial exp2
+#endif
+#ifndef B200_EMU_ALT
+#define B200_EMU_ALT 1      // spread them over the row instead of taking the first ones of every 16
 #endif
 
 namespace {
@@ -64,12 +84,17 @@ namespace tc {
 constexpr int kD = 128;            // head dim the tiles are laid out for (kHD = 64 uses the first 64-wide half)
 constexpr int kBlockKV = 128;      // kv tokens per MMA block
 constexpr int kQTiles = 2;
-constexpr int kSplit = 2;                            // threads per MMA row in the softmax (columns split between them)
-constexpr int kSoftmaxWarps = 4 * kSplit;            // all of them work on every query tile
+constexpr int kSoftmaxWarps = 4;                     // per query tile
 constexpr int kMmaWarp = 8;
 constexpr int kProducerWarp0 = 12;
 constexpr int kProducerWarps = 4;
 constexpr int kProducerThreads = kProducerWarps * 32;
+#ifndef B200_ROWS_WARP0
+#define B200_ROWS_WARP0 8
+#endif
+constexpr int kRowsWarp0 = B200_ROWS_WARP0;          // K/V rows per block gathered by the producer warp next to the MMA warp
+constexpr int kRowsOther = (kBlockKV - kRowsWarp0) / 3;
+static_assert(kRowsWarp0 % 8 == 0 && kRowsOther % 8 == 0 && kRowsWarp0 + 3 * kRowsOther == kBlockKV, "row split");
 constexpr int kThreads = 512;
 
 constexpr int kRowBytes = kD * 2;                    // one K/V/Q row of one head (16-bit elements)
@@ -85,7 +110,7 @@ constexpr int kTmemS = 0, kTmemO = 256;
 constexpr int kRegsSoftmax = 200, kRegsOther = 56;   // 256 x 200 + 256 x 56 = 64 Ki registers
 // Of every 8 column pairs, this many take the polynomial exp2 on the FMA pipe instead of MUFU.EX2 (16/clk/SM would
 // otherwise cost as many cycles as the MMAs); tuned on B200, both paths agree to 1e-4 relative.
-constexpr int kEmuEighths = 3;
+constexpr int kEmuEighths = B200_EMU;
 
 // Shared-memory map and barrier slots.  16-bit pools: 5 ring slots.  FP8 pools: 4 ring slots (the MMA
 // operands are f16 tiles the producers write) + 2 raw 16 KiB landing buffers for the cp.async gathers.
@@ -97,9 +122,7 @@ struct Layout {
   static constexpr int kSmemKV = kSmemQ + kQTiles * kQTileBytes;
   static constexpr int kSmemRaw = kSmemKV + kSlots * kSlotBytes;
   static constexpr int kSmemBar = kSmemRaw + kRawBufs * kRawBytes;
-  static constexpr int kSmemXchg = kSmemBar + 256;             // row-max / row-sum exchange of the softmax threads
-  static constexpr int kXchgBytes = kQTiles * kSplit * 128 * 2;
-  static constexpr int kSmemBytes = kSmemXchg + kXchgBytes + 1024;   // + slack for the 1024-byte alignment
+  static constexpr int kSmemBytes = kSmemBar + 256 + 1024;    // barriers + slack for the 1024-byte alignment
   // barrier slots (8 bytes each)
   static constexpr int kBarQFull = 0;
   static constexpr int kBarFull = 1;                     // kSlots
