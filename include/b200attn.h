@@ -393,7 +393,7 @@ typedef struct b200_oproj_allreduce_args {
   int64_t staging_bytes;     /* bytes of ONE staging buffer; the staging area holds two (alternating by launch) */
   int32_t mode;              /* B200_OAR_AUTO / ONE_SHOT (every rank reduces every tile itself: shortest chain,
                                 world x the output over the fabric) / TWO_SHOT (tile owner reduces + broadcasts) */
-  void* debug_times;         /* optional uint64 [tiles][8]: %globaltimer at the epilogue's phase boundaries (tuning aid) */
+  void* debug_times;         /* optional uint64 [tiles][8]: %globaltimer at the epilogue's phase boundaries; written by -DB200_DEV builds only */
 } b200_oproj_allreduce_args;
 
 int b200attn_oproj_allreduce(const b200_oproj_allreduce_args* args, b200_stream_t stream);

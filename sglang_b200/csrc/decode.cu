@@ -414,14 +414,19 @@ extern "C" int b200attn_decode_fast_supported(int32_t dqk, int32_t dv, int32_t g
 
 namespace b200 {
 namespace {
-// B200ATTN_DECODE_HG=0 forces the per-head kernel (A/B measurements); default on.
+// -DB200_DEV builds only: B200ATTN_DECODE_HG=0 forces the per-head kernel (A/B measurements).  The shipped library
+// reads no environment variable on a launch path.
 bool decode_hg_enabled() {
+#ifdef B200_DEV
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("B200ATTN_DECODE_HG");
     v = (e && e[0] == '0') ? 0 : 1;
   }
   return v != 0;
+#else
+  return true;
+#endif
 }
 bool decode_hg_shape_ok(int hq, int hkv, int dqk, int dv, int q_dtype, int kv_dtype) {
   if (!decode_hg_enabled() || hkv <= 0 || hq % hkv != 0 || hkv % kHG != 0) return false;

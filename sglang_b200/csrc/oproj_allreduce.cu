@@ -269,7 +269,11 @@ __global__ void __launch_bounds__(oar::kThreads, 1) oproj_allreduce_kernel(const
       const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
       const int m0 = tm * BM, n0 = tn * BN;
       const int rows = min(BM, p.T - m0);
+#ifdef B200_DEV
       unsigned long long* dbg = (p.debug_times != nullptr && et == 0) ? p.debug_times + (int64_t)tile * 8 : nullptr;
+#else
+      unsigned long long* const dbg = nullptr;             // phase stamps exist in -DB200_DEV builds only
+#endif
       if (dbg) dbg[0] = globaltimer_ns();
       mbar_wait(bar(kBarAccFull), it & 1, 40);
       if (dbg) dbg[1] = globaltimer_ns();
@@ -410,13 +414,18 @@ __global__ void __launch_bounds__(oar::kThreads, 1) oproj_allreduce_kernel(const
   }
 }
 
+// -DB200_DEV builds only: B200ATTN_OAR_MULTICAST=0 forces the peer-load exchange (A/B measurements)
 bool oar_mc_enabled() {
+#ifdef B200_DEV
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("B200ATTN_OAR_MULTICAST");
     v = (e && e[0] == '0') ? 0 : 1;
   }
   return v != 0;
+#else
+  return true;
+#endif
 }
 
 }  // namespace
@@ -493,11 +502,13 @@ extern "C" int b200attn_oproj_allreduce(const b200_oproj_allreduce_args* a, b200
   p.a_rows = ((p.T < BM ? p.T : BM) + 7) / 8 * 8;
   p.stages = (kSmemBudget - kATile) / (kBTile + p.a_rows * 256);
   if (p.stages > kMaxStages) p.stages = kMaxStages;
+#ifdef B200_DEV
   {
-    static int cap = -1;                                   // B200ATTN_OAR_STAGES: tuning aid
+    static int cap = -1;                                   // B200ATTN_OAR_STAGES: tuning aid of dev builds
     if (cap < 0) { const char* e = getenv("B200ATTN_OAR_STAGES"); cap = e ? atoi(e) : 0; }
     if (cap >= 2 && cap < p.stages) p.stages = cap;
   }
+#endif
   const int smem_bytes = p.stages * (kBTile + p.a_rows * 256) + kATile + 512 + 1024;
   const int kSmemMax = 227 * 1024;
   const int grid = n_tiles < sm_count() ? n_tiles : sm_count();   // every CTA resident: peers wait on each other

@@ -400,13 +400,18 @@ __global__ void __launch_bounds__(kRopeWarps * 32) rope_store_fast_kernel(const 
   }
 }
 
+// -DB200_DEV builds only: B200ATTN_ROPE_FAST=0 forces the generic kernel (A/B measurements)
 inline bool rope_fast_enabled() {
+#ifdef B200_DEV
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("B200ATTN_ROPE_FAST");
     v = (e && e[0] == '0') ? 0 : 1;
   }
   return v != 0;
+#else
+  return true;
+#endif
 }
 
 template <typename SRC, typename DST, int D, bool NEOX>
