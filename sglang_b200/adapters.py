@@ -120,8 +120,8 @@ class B200RowParallelLinear(torch.nn.Module):
                                        requires_grad=False) if bias else None
         #: largest T that takes the fused kernel; above it cuBLAS + NCCL is faster
         self.fused_max_tokens = int(fused_max_tokens)
-        self._comm = OProjAllReduce(min(max_tokens, self.fused_max_tokens), output_size, dtype, device=device,
-                                    group=group if tp_size > 1 else None)
+        self._comm = OProjAllReduce(group if tp_size > 1 else None, min(max_tokens, self.fused_max_tokens), output_size,
+                                    dtype, device)
 
     def forward(self, input_: torch.Tensor, skip_all_reduce: bool = False, forward_batch=None,
                 output_tensor: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:

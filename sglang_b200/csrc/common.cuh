@@ -7,6 +7,7 @@
 #include <stdint.h>
 
 #include <atomic>
+#include <utility>
 #include <cstdarg>
 #include <cstdio>
 
@@ -51,8 +52,32 @@ inline cudaError_t set_max_dynamic_smem(Kern kern, int bytes, std::atomic<uint64
   return e;
 }
 
+// Programmatic dependent launch (PDL): the kernels of the per-layer decode chain (store -> attention -> merge) are
+// launched with cudaLaunchAttributeProgrammaticStreamSerialization, call pdl_launch_dependents() first thing and
+// pdl_wait() before they touch global memory.  The next kernel's CTAs are then resident (launch latency paid) while
+// the previous grid still runs; griddepcontrol.wait returns once every prerequisite grid has completed and its
+// writes are visible, so the data flow is the stream order's.  Launched without the attribute both are no-ops.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+
 // -------------------------------------------------------------- device side
 constexpr int kWarp = 32;
+
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 struct e4m3_t { uint8_t x; };
 struct e5m2_t { uint8_t x; };

@@ -17,7 +17,7 @@ constexpr int kHG = 4;   // kv heads per work item == warps per CTA
 
 template <int D, int KV>
 struct HgCfg {
-  static constexpr bool kFp8 = KV == B200_FP8_E4M3;
+  static constexpr bool kFp8 = KV == B200_FP8_E4M3 || KV == B200_FP8_E5M2;
   static constexpr int kEsz = kFp8 ? 1 : 2;
   static constexpr int kRowB = D * kEsz;                 // one head's K (or V) row
   static constexpr int kCpr = kRowB / 16;                // 16-byte chunks per head row
@@ -37,6 +37,8 @@ struct HgCfg {
 
 template <int D, int KV, typename QT, bool UPPER>
 __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_hg_kernel(const DecodeParams p) {
+  pdl_launch_dependents();          // the merge kernel's CTAs may become resident now
+  pdl_wait();                       // the KV store of this layer (and the planner) have completed
   using C = HgCfg<D, KV>;
   using CT = typename std::conditional<C::kFp8, __half, QT>::type;  // MMA operand type
   extern __shared__ __align__(128) uint8_t smem[];
@@ -183,9 +185,9 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
           for (int u = 0; u < 2; ++u) {
             const int ks = c2 + u;
             mma16816<CT>(s_acc[0], QA(ks, 0), QA(ks, 1), QA(ks, 2), QA(ks, 3),
-                         e4m3x2_to_f16x2(b[2 * u] & 0xffffu), e4m3x2_to_f16x2(b[2 * u] >> 16));
+                         fp8x2_to_f16x2<KV>(b[2 * u] & 0xffffu), fp8x2_to_f16x2<KV>(b[2 * u] >> 16));
             mma16816<CT>(s_acc[1], QA(ks, 0), QA(ks, 1), QA(ks, 2), QA(ks, 3),
-                         e4m3x2_to_f16x2(b[2 * u + 1] & 0xffffu), e4m3x2_to_f16x2(b[2 * u + 1] >> 16));
+                         fp8x2_to_f16x2<KV>(b[2 * u + 1] & 0xffffu), fp8x2_to_f16x2<KV>(b[2 * u + 1] >> 16));
           }
         }
       }
@@ -270,10 +272,10 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
             // bytes [t0 d, t0 d+1, t1 d, t1 d+1] -> [t0 d, t1 d | t0 d+1, t1 d+1]
             const uint32_t x0 = prmt(b[2 * u], 0u, 0x3120u), x1 = prmt(b[2 * u + 1], 0u, 0x3120u);
             const int nt = 2 * (j + u);
-            mma16816<CT>(o[nt], pa[0], pa[1], pa[2], pa[3], e4m3x2_to_f16x2(x0 & 0xffffu),
-                         e4m3x2_to_f16x2(x1 & 0xffffu));
-            mma16816<CT>(o[nt + 1], pa[0], pa[1], pa[2], pa[3], e4m3x2_to_f16x2(x0 >> 16),
-                         e4m3x2_to_f16x2(x1 >> 16));
+            mma16816<CT>(o[nt], pa[0], pa[1], pa[2], pa[3], fp8x2_to_f16x2<KV>(x0 & 0xffffu),
+                         fp8x2_to_f16x2<KV>(x1 & 0xffffu));
+            mma16816<CT>(o[nt + 1], pa[0], pa[1], pa[2], pa[3], fp8x2_to_f16x2<KV>(x0 >> 16),
+                         fp8x2_to_f16x2<KV>(x1 >> 16));
           }
         }
       }
@@ -335,7 +337,7 @@ bool decode_hg_supported(const DecodeParams& p, int q_dtype, int kv_dtype) {
   if (p.num_kv_heads % kHG != 0) return false;
   if (!decode_fast_supported(D, p.head_dim_v, p.group, q_dtype, kv_dtype)) return false;
   if (D == 256 && kv_dtype != B200_FP8_E4M3) return false;     // 192 KiB ring: keep the per-head kernel
-  const int esz = kv_dtype == B200_FP8_E4M3 ? 1 : 2;
+  const int esz = (kv_dtype == B200_FP8_E4M3 || kv_dtype == B200_FP8_E5M2) ? 1 : 2;
   // the 4 heads of a group must be contiguous in a pool row; outputs must take 8-byte vector stores
   return p.k_stride_h == D && p.v_stride_h == D && (p.k_stride_s * esz) % 16 == 0 && (p.v_stride_s * esz) % 16 == 0 &&
          p.o_stride_t % 4 == 0 && p.o_stride_h % 4 == 0 && ((uintptr_t)p.o & 7) == 0;
@@ -347,9 +349,10 @@ int launch_decode_hg_inst(const DecodeParams& p, int num_ctas, cudaStream_t stre
   static std::atomic<uint64_t> configured{0};
   auto kern = decode_hg_kernel<D, KV, QT, UPPER>;
   B200_CHECK_CUDA(set_max_dynamic_smem(kern, C::kCtaSmem, configured));
-  kern<<<num_ctas, kHG * kWarp, C::kCtaSmem, stream>>>(p);
+  B200_CHECK_CUDA(launch_pdl(kern, dim3(num_ctas), dim3(kHG * kWarp), C::kCtaSmem, stream, p));
   B200_CHECK_CUDA(cudaGetLastError());
-  decode_merge_fast_kernel<QT, D><<<p.batch_size * p.num_q_heads, kFastWarps * kWarp, 0, stream>>>(p);
+  B200_CHECK_CUDA(launch_pdl(decode_merge_fast_kernel<QT, D>, dim3(p.batch_size * p.num_q_heads), dim3(kFastWarps * kWarp), 0,
+                             stream, p));
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;
 }
@@ -367,6 +370,8 @@ int launch_decode_hg_q(const DecodeParams& p, int kv_dtype, int num_ctas, cudaSt
   if (kv_dtype == B200_FP8_E4M3) {
     if (D == 128) return launch_decode_hg_d<128, B200_FP8_E4M3, QT>(p, num_ctas, stream);
     if (D == 256) return launch_decode_hg_d<256, B200_FP8_E4M3, QT>(p, num_ctas, stream);
+  } else if (kv_dtype == B200_FP8_E5M2) {
+    if (D == 128) return launch_decode_hg_d<128, B200_FP8_E5M2, QT>(p, num_ctas, stream);
   } else {
     if (D == 64) return launch_decode_hg_d<64, kSame, QT>(p, num_ctas, stream);
     if (D == 128) return launch_decode_hg_d<128, kSame, QT>(p, num_ctas, stream);
@@ -382,7 +387,7 @@ int launch_decode_hg(const DecodeParams& p, int q_dtype, int kv_dtype, int num_c
 
 // resident CTAs per SM of the instance the dispatcher would pick (grid = SMs x this)
 int decode_hg_ctas_per_sm(int head_dim, int kv_dtype) {
-  const bool fp8 = kv_dtype == B200_FP8_E4M3;
+  const bool fp8 = kv_dtype == B200_FP8_E4M3 || kv_dtype == B200_FP8_E5M2;
   const int stage = 2 * kTileTok * kHG * head_dim * (fp8 ? 1 : 2);
   const int smem = (stage <= 16 * 1024 ? 4 : 3) * stage;
   return smem > 110 * 1024 ? 1 : (smem <= 72 * 1024 ? 3 : 2);

@@ -52,20 +52,26 @@ __device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
   }
 }
-__device__ __forceinline__ uint32_t e4m3x2_to_f16x2(uint32_t two_bytes) {
-  uint32_t r;
-  asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(r) : "h"((uint16_t)two_bytes));
-  return r;
-}
 __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
   uint32_t r;
   asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
   return r;
 }
+// two FP8 bytes (low half of the argument) -> f16x2, exact for both formats: e4m3 through the hardware converter,
+// e5m2 by byte placement (an e5m2 byte is the high byte of its f16)
+template <int KV> __device__ __forceinline__ uint32_t fp8x2_to_f16x2(uint32_t two_bytes) {
+  if constexpr (KV == B200_FP8_E5M2) {
+    return prmt(two_bytes, 0u, 0x1404);
+  } else {
+    uint32_t r;
+    asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(r) : "h"((uint16_t)two_bytes));
+    return r;
+  }
+}
 
 template <int D, int KV>
 struct FastCfg {
-  static constexpr bool kFp8 = KV == B200_FP8_E4M3;
+  static constexpr bool kFp8 = KV == B200_FP8_E4M3 || KV == B200_FP8_E5M2;
   static constexpr int kEsz = kFp8 ? 1 : 2;
   static constexpr int kRowB = D * kEsz;                 // bytes of one K (or V) row of one head
   static constexpr int kCpr = kRowB / 16;                // 16-byte chunks per row
@@ -86,6 +92,8 @@ struct FastCfg {
 // combined through shared memory, so even 100+ chunks cost only a few dependent L2 round trips.
 template <typename QT, int D>
 __global__ void __launch_bounds__(kFastWarps* kWarp) decode_merge_fast_kernel(const DecodeParams p) {
+  pdl_launch_dependents();          // next layer's KV store
+  pdl_wait();                       // every partial of this layer has been written
   constexpr int kVec = D / 32;
   __shared__ float s_acc[kFastWarps][D];
   __shared__ float s_ml[kFastWarps][2];
@@ -150,6 +158,8 @@ __global__ void __launch_bounds__(kFastWarps* kWarp) decode_merge_fast_kernel(co
 template <int D, int KV, typename QT, bool UPPER>
 __global__ void __launch_bounds__(kFastWarps* kWarp, (FastCfg<D, KV>::kCtaSmem > 110 * 1024) ? 1 : ((FastCfg<D, KV>::kCtaSmem <= 72 * 1024) ? 3 : 2))
     decode_mma_kernel(const DecodeParams p) {
+  pdl_launch_dependents();          // the merge kernel's CTAs may become resident now
+  pdl_wait();                       // the KV store of this layer (and the planner) have completed
   using C = FastCfg<D, KV>;
   using CT = typename std::conditional<C::kFp8, __half, QT>::type;  // MMA operand type
   constexpr int kRows = UPPER ? 16 : 8;
@@ -289,9 +299,9 @@ __global__ void __launch_bounds__(kFastWarps* kWarp, (FastCfg<D, KV>::kCtaSmem >
           for (int u = 0; u < 2; ++u) {
             const int ks = c2 + u;
             mma16816<CT>(s_acc[0], QA(ks, 0), QA(ks, 1), QA(ks, 2), QA(ks, 3),
-                         e4m3x2_to_f16x2(b[2 * u] & 0xffffu), e4m3x2_to_f16x2(b[2 * u] >> 16));
+                         fp8x2_to_f16x2<KV>(b[2 * u] & 0xffffu), fp8x2_to_f16x2<KV>(b[2 * u] >> 16));
             mma16816<CT>(s_acc[1], QA(ks, 0), QA(ks, 1), QA(ks, 2), QA(ks, 3),
-                         e4m3x2_to_f16x2(b[2 * u + 1] & 0xffffu), e4m3x2_to_f16x2(b[2 * u + 1] >> 16));
+                         fp8x2_to_f16x2<KV>(b[2 * u + 1] & 0xffffu), fp8x2_to_f16x2<KV>(b[2 * u + 1] >> 16));
           }
         }
       }
@@ -376,10 +386,10 @@ __global__ void __launch_bounds__(kFastWarps* kWarp, (FastCfg<D, KV>::kCtaSmem >
             // bytes [t0 d, t0 d+1, t1 d, t1 d+1] -> [t0 d, t1 d | t0 d+1, t1 d+1]
             const uint32_t x0 = prmt(b[2 * u], 0u, 0x3120u), x1 = prmt(b[2 * u + 1], 0u, 0x3120u);
             const int nt = 2 * (j + u);
-            mma16816<CT>(o[nt], pa[0], pa[1], pa[2], pa[3], e4m3x2_to_f16x2(x0 & 0xffffu),
-                         e4m3x2_to_f16x2(x1 & 0xffffu));
-            mma16816<CT>(o[nt + 1], pa[0], pa[1], pa[2], pa[3], e4m3x2_to_f16x2(x0 >> 16),
-                         e4m3x2_to_f16x2(x1 >> 16));
+            mma16816<CT>(o[nt], pa[0], pa[1], pa[2], pa[3], fp8x2_to_f16x2<KV>(x0 & 0xffffu),
+                         fp8x2_to_f16x2<KV>(x1 & 0xffffu));
+            mma16816<CT>(o[nt + 1], pa[0], pa[1], pa[2], pa[3], fp8x2_to_f16x2<KV>(x0 >> 16),
+                         fp8x2_to_f16x2<KV>(x1 >> 16));
           }
         }
       }
@@ -452,12 +462,13 @@ bool decode_fast_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype
   if (q_dtype != B200_BF16 && q_dtype != B200_F16) return false;
   if (kv_dtype == q_dtype) return true;
   if (kv_dtype == B200_FP8_E4M3) return dqk >= 128;
+  if (kv_dtype == B200_FP8_E5M2) return dqk == 128;
   return false;
 }
 
 int decode_fast_ctas_per_sm(int head_dim, int kv_dtype) {
   if (head_dim >= 256) return 1;
-  return (kv_dtype == B200_FP8_E4M3 && head_dim == 128) ? 3 : 2;
+  return ((kv_dtype == B200_FP8_E4M3 || kv_dtype == B200_FP8_E5M2) && head_dim == 128) ? 3 : 2;
 }
 
 bool decode_fast_layout_ok(const DecodeParams& p, int kv_dtype) {
@@ -474,9 +485,10 @@ int launch_decode_fast_inst(const DecodeParams& p, int num_ctas, cudaStream_t st
   static std::atomic<uint64_t> configured{0};
   auto kern = decode_mma_kernel<D, KV, QT, UPPER>;
   B200_CHECK_CUDA(set_max_dynamic_smem(kern, C::kCtaSmem, configured));
-  kern<<<num_ctas, kFastWarps * kWarp, C::kCtaSmem, stream>>>(p);
+  B200_CHECK_CUDA(launch_pdl(kern, dim3(num_ctas), dim3(kFastWarps * kWarp), C::kCtaSmem, stream, p));
   B200_CHECK_CUDA(cudaGetLastError());
-  decode_merge_fast_kernel<QT, D><<<p.batch_size * p.num_q_heads, kFastWarps * kWarp, 0, stream>>>(p);
+  B200_CHECK_CUDA(launch_pdl(decode_merge_fast_kernel<QT, D>, dim3(p.batch_size * p.num_q_heads), dim3(kFastWarps * kWarp), 0,
+                             stream, p));
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;
 }
@@ -494,6 +506,8 @@ int launch_decode_fast_q(const DecodeParams& p, int kv_dtype, int num_ctas, cuda
   if (kv_dtype == B200_FP8_E4M3) {
     if (D == 128) return launch_decode_fast_d<128, B200_FP8_E4M3, QT>(p, num_ctas, stream);
     if (D == 256) return launch_decode_fast_d<256, B200_FP8_E4M3, QT>(p, num_ctas, stream);
+  } else if (kv_dtype == B200_FP8_E5M2) {
+    if (D == 128) return launch_decode_fast_d<128, B200_FP8_E5M2, QT>(p, num_ctas, stream);
   } else {
     if (D == 64) return launch_decode_fast_d<64, kSame, QT>(p, num_ctas, stream);
     if (D == 128) return launch_decode_fast_d<128, kSame, QT>(p, num_ctas, stream);

@@ -163,6 +163,8 @@ __device__ __forceinline__ void move_scalar(const SRC* src, DST* dst, int n, int
 // back to back (the slot lookup, needed only for the stores, overlaps them).
 template <typename SRC, typename DST, bool kVecOK>
 __global__ void __launch_bounds__(kStoreWarps* kWarp) store_kv_kernel(const StoreParams p) {
+  pdl_launch_dependents();          // the next kernel of the layer (attention) may take its seats
+  pdl_wait();                       // ... while this one waits for whatever ran before it
   const int lane = threadIdx.x & 31;
   const int64_t warp = (int64_t)blockIdx.x * kStoreWarps + (threadIdx.x >> 5);
   const int64_t token = warp / p.segs;
@@ -219,9 +221,9 @@ int launch_store(const b200_store_kv_args& a, cudaStream_t stream) {
                       aligned(a.k, 16) && aligned(a.v, 16) &&
                       aligned(a.k_cache, sizeof(DST) * kVec) && aligned(a.v_cache, sizeof(DST) * kVec);
   if (vec_ok) {
-    store_kv_kernel<SRC, DST, true><<<(unsigned)blocks, kStoreWarps * kWarp, 0, stream>>>(p);
+    B200_CHECK_CUDA(launch_pdl(store_kv_kernel<SRC, DST, true>, dim3((unsigned)blocks), dim3(kStoreWarps * kWarp), 0, stream, p));
   } else {
-    store_kv_kernel<SRC, DST, false><<<(unsigned)blocks, kStoreWarps * kWarp, 0, stream>>>(p);
+    B200_CHECK_CUDA(launch_pdl(store_kv_kernel<SRC, DST, false>, dim3((unsigned)blocks), dim3(kStoreWarps * kWarp), 0, stream, p));
   }
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;

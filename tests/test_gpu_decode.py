@@ -93,6 +93,24 @@ def test_decode_vs_oracle(shape, dtype, pool_dtype, kernel):
     assert_close_scaled(got, want)
 
 
+@pytest.mark.parametrize("shape", [(3, 32, 8, 128, [1, 17, 600], 1), (5, 8, 1, 128, [2048, 33, 700, 64, 65], 16),
+                                   (2, 16, 1, 128, [300, 129], 1)], ids=["hg_8B", "perhead_70Btp8", "group16"])
+def test_decode_e5m2_fast_kernels(shape):
+    """FP8-e5m2 pools (--kv-cache-dtype fp8_e5m2) on the tensor-core decode kernels (head-group and per-head)."""
+    from sglang_b200 import _C
+
+    bs, Hq, Hkv, D, lens, page = shape
+    pool_dtype = torch.float8_e5m2
+    assert _C.lib.b200attn_decode_fast_supported(D, D, Hq // Hkv, _C.B200_BF16, _C.B200_FP8_E5M2) == 1
+    q, kp, vp, rtt, rpi, seq = _random_problem(bs, Hq, Hkv, D, lens, page, torch.bfloat16, pool_dtype, seed=7)
+    want = ref.decode_ref(q, kp, vp, rtt, rpi, seq, D**-0.5, kv_dtype=pool_dtype)
+    for kernel in (2, 0):                       # KERNEL_FAST (refuses shapes it does not cover), KERNEL_AUTO
+        got, _ = _run_ops_decode(q, kp, vp, rtt, rpi, seq, D**-0.5, pool_dtype, kernel=kernel)
+        assert_close_scaled(got, want, f"kernel {kernel}")
+    gen, _ = _run_ops_decode(q, kp, vp, rtt, rpi, seq, D**-0.5, pool_dtype, kernel=KERNELS["generic"])
+    assert float((got - gen).abs().max()) <= 2e-2
+
+
 def test_decode_fp8_descale_and_logit_cap():
     q, kp, vp, rtt, rpi, seq = _random_problem(3, 8, 2, 128, [400, 3, 129], 1, torch.bfloat16,
                                                torch.float8_e4m3fn, seed=11)
