@@ -158,6 +158,7 @@ __global__ void __launch_bounds__(oar::kThreads, 1) oproj_allreduce_kernel(const
   const uint32_t smem_bar = smem_a + kStages * a_stage + kATile;
   auto bar = [&](int i) -> uint32_t { return smem_bar + 8 * i; };
   const uint32_t tmem_slot = smem_bar + 8 * kNumBars;
+  pdl_launch_dependents();
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -175,6 +176,34 @@ __global__ void __launch_bounds__(oar::kThreads, 1) oproj_allreduce_kernel(const
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
+  const int n_tiles = p.tiles_m * p.tiles_n;
+  const int n_kb = p.K / BK;
+  const int64_t row_bytes = (int64_t)p.N * 2;            // staging / output rows: [T, N] in the model dtype
+
+  // Programmatic dependent launch: this kernel may become resident while the attention kernels before it still run.
+  // The weights do not depend on them, so the producers fill the w half of the first ring stages right away; x
+  // (the attention output), the epoch and every flag are read only after griddepcontrol.wait.
+  int w_prefetched = 0;                                     // ring steps whose w tile is already in flight
+  if (warp >= kProdWarp0) {
+    const int pt = threadIdx.x - kProdWarp0 * 32;
+    const int chunk = pt & 15, r0 = pt >> 4;
+    const uint32_t swz_lo = (uint32_t)(chunk & 7), blk = (uint32_t)(chunk >> 3);
+    for (int tile = blockIdx.x; tile < n_tiles && w_prefetched < kStages; tile += gridDim.x) {
+      const int n0 = (tile % p.tiles_n) * BN;
+      const uint8_t* wb = reinterpret_cast<const uint8_t*>(p.w) + ((int64_t)n0 * p.w_stride) * 2 + chunk * 16;
+      for (int kb = 0; kb < n_kb && w_prefetched < kStages; ++kb, ++w_prefetched) {
+        const uint32_t b_dst = smem_base + w_prefetched * kBTile + blk * (kBTile / 2);
+#pragma unroll
+        for (int i = 0; i < BN / 8; ++i) {
+          const int row = i * 8 + r0;
+          cp_async16_full(b_dst + row * 128 + ((swz_lo ^ (row & 7)) << 4),
+                          wb + (int64_t)row * p.w_stride * 2 + (int64_t)kb * BK * 2);
+        }
+      }
+    }
+  }
+  pdl_wait();
+
   // The epoch lives in device memory so that a CUDA-graph replay (same kernel arguments) still gets a fresh one:
   // every CTA reads it at start, the last CTA to finish bumps it.  Every rank launches the same sequence, so the
   // epochs agree across ranks without any host involvement.
@@ -185,10 +214,6 @@ __global__ void __launch_bounds__(oar::kThreads, 1) oproj_allreduce_kernel(const
   // them when that peer starts launch n + 2, because launch n + 1 needed this rank's arrive flags.
   const int64_t stage_off = (epoch & 1u) ? p.staging_bytes : 0;
 
-  const int n_tiles = p.tiles_m * p.tiles_n;
-  const int n_kb = p.K / BK;
-  const int64_t row_bytes = (int64_t)p.N * 2;            // staging / output rows: [T, N] in the model dtype
-
   if (warp >= kProdWarp0) {
     // ------------------------------------------------------------------ producers: x and w tiles -> smem ring
     // A k-block is BK = 128 elements = 256 bytes per row = two 128-byte swizzle blocks side by side: 16 lanes
@@ -198,6 +223,7 @@ __global__ void __launch_bounds__(oar::kThreads, 1) oproj_allreduce_kernel(const
     const uint32_t a_half = a_stage >> 1;                    // bytes of one swizzle block of an x tile
     const uint32_t swz_lo = (uint32_t)(chunk & 7), blk = (uint32_t)(chunk >> 3);
     uint32_t s = 0, round = 0;                               // ring slot and how often the ring has wrapped
+    int step = 0;                                            // k-blocks issued so far (the first w_prefetched have their w)
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
       const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
       const int m0 = tm * BM, n0 = tn * BN;
@@ -207,10 +233,12 @@ __global__ void __launch_bounds__(oar::kThreads, 1) oproj_allreduce_kernel(const
         if (round > 0) mbar_wait(bar(kBarEmpty + s), (round - 1) & 1, 10 + s);
         const uint32_t a_dst = smem_a + s * a_stage + blk * a_half, b_dst = smem_base + s * kBTile + blk * (kBTile / 2);
         const int64_t koff = (int64_t)kb * BK * 2;
+        if (step++ >= w_prefetched) {
 #pragma unroll
-        for (int i = 0; i < BN / 8; ++i) {
-          const int row = i * 8 + r0;
-          cp_async16_full(b_dst + row * 128 + ((swz_lo ^ (row & 7)) << 4), wb + (int64_t)row * p.w_stride * 2 + koff);
+          for (int i = 0; i < BN / 8; ++i) {
+            const int row = i * 8 + r0;
+            cp_async16_full(b_dst + row * 128 + ((swz_lo ^ (row & 7)) << 4), wb + (int64_t)row * p.w_stride * 2 + koff);
+          }
         }
 #pragma unroll
         for (int i = 0; i < BM / 8; ++i) {
@@ -517,12 +545,12 @@ extern "C" int b200attn_oproj_allreduce(const b200_oproj_allreduce_args* a, b200
     static std::atomic<uint64_t> configured{0};
     auto kern = oproj_allreduce_kernel<__nv_bfloat16>;
     B200_CHECK_CUDA(set_max_dynamic_smem(kern, kSmemMax, configured));
-    kern<<<grid, kThreads, smem_bytes, stream>>>(p);
+    B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), smem_bytes, stream, p));
   } else {
     static std::atomic<uint64_t> configured{0};
     auto kern = oproj_allreduce_kernel<__half>;
     B200_CHECK_CUDA(set_max_dynamic_smem(kern, kSmemMax, configured));
-    kern<<<grid, kThreads, smem_bytes, stream>>>(p);
+    B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), smem_bytes, stream, p));
   }
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;
