@@ -93,8 +93,9 @@ constexpr int kProducerThreads = kProducerWarps * 32;
 #define B200_ROWS_WARP0 8
 #endif
 constexpr int kRowsWarp0 = B200_ROWS_WARP0;          // K/V rows per block gathered by the producer warp next to the MMA warp
-constexpr int kRowsOther = (kBlockKV - kRowsWarp0) / 3;
-static_assert(kRowsWarp0 % 8 == 0 && kRowsOther % 8 == 0 && kRowsWarp0 + 3 * kRowsOther == kBlockKV, "row split");
+constexpr int kRowsOther = (kBlockKV - kRowsWarp0) / 3;   // (0: the others take 48 / 40 / 40)
+static_assert(kRowsWarp0 == 0 || (kRowsWarp0 % 8 == 0 && kRowsOther % 8 == 0 && kRowsWarp0 + 3 * kRowsOther == kBlockKV),
+              "row split");
 constexpr int kThreads = 512;
 
 constexpr int kRowBytes = kD * 2;                    // one K/V/Q row of one head (16-bit elements)
