@@ -97,7 +97,7 @@ def decode_case(name, bs, L, Hq, Hkv, D, pool_dtype, page, iters, ragged=False):
 
 
 def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_dtype=torch.bfloat16, tree_mask=False,
-                page=1):
+                page=1, one_tile=False):
     """`page` > 1: the pool is page-granular (random page order, slots consecutive inside a page -- what SGLang's
     paged allocator hands out); P and E must be multiples of it."""
     dev = "cuda"
@@ -127,6 +127,8 @@ def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_d
     ext = torch.full((bs,), E, dtype=torch.int32, device=dev)
     sm, _, _ = ops.device_info()
     bq = ops.extend_block_q(D, D, Hq // Hkv, torch.bfloat16, pool_dtype, kernel)
+    if one_tile:        # what the backend plans when no request extends by more than 128 / group tokens
+        bq = ops.extend_block_q_one_tile(D, D, Hq // Hkv, torch.bfloat16, pool_dtype, kernel)
     ws = ops.ExtendWorkspace.create(bs, T // bq + bs + 1, dev, num_ctas=sm)
     ops.extend_plan(ws, ext, bq, page_size=page, req_to_token=rtt, req_pool_indices=rpi, extend_prefix_lens=pre)
 
@@ -235,8 +237,15 @@ def main():
         emit(extend_case("cfg5/16 with FP8-e5m2 KV pool", 8, 16384, 1024, 32, 8, 128, it, pool_dtype=torch.float8_e5m2))
         emit(extend_case("prefill 8 req x 4K no prefix", 8, 0, 4096, 32, 8, 128, it))
         emit(extend_case("70B tp8 4 req x (8K + 2K)", 4, 8192, 2048, 8, 1, 128, it))
-        emit(extend_case("verify 64 req x (4K + 8 draft, tree mask), tcgen05", 64, 4096, 8, 32, 8, 128, it,
+        emit(extend_case("verify 64 req x (4K + 8 draft, tree mask), tcgen05 two-tile items", 64, 4096, 8, 32, 8, 128, it,
                          shared=False, tree_mask=True))
+        emit(extend_case("verify 64 req x (4K + 8 draft, tree mask), tcgen05 one-tile items (backend's choice)", 64,
+                         4096, 8, 32, 8, 128, it, shared=False, tree_mask=True, one_tile=True))
+        emit(extend_case("short extend 64 req x (4K + 16 new), one-tile items", 64, 4096, 16, 32, 8, 128, it,
+                         shared=False, one_tile=True))
+        emit(extend_case("short extend 64 req x (4K + 16 new), two-tile items", 64, 4096, 16, 32, 8, 128, it,
+                         shared=False))
+        emit(extend_case("cfg5/16 with one-tile items (for reference)", 8, 16384, 1024, 32, 8, 128, it, one_tile=True))
         emit(extend_case("verify 64 req x (4K + 8 draft, tree mask), generic", 64, 4096, 8, 32, 8, 128, 3,
                          shared=False, tree_mask=True, kernel=1))
         emit(extend_case("D64 qwen2.5-0.5b heads 8 req x (16K shared prefix + 1K)", 8, 16384, 1024, 14, 2, 64, it))

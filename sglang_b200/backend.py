@@ -140,6 +140,12 @@ class B200AttnBackend(_Base):
         group = self.num_head // self.num_kv_head
         self._extend_block_q = ops.extend_block_q(self.head_dim, self.v_head_dim, group, self._q_dtype,
                                                   self.kv_dtype, self.extend_kernel)
+        # short extends (TARGET_VERIFY, DRAFT_EXTEND, a few new tokens behind a cached prefix): when no request
+        # extends by more than one 128-row tile of tokens, plan one-tile items -- the tcgen05 kernel then runs its
+        # one-tile instance instead of carrying an empty second tile (0 = that instance does not apply)
+        self._one_tile_block_q = ops.extend_block_q_one_tile(self.head_dim, self.v_head_dim, group, self._q_dtype,
+                                                             self.kv_dtype, self.extend_kernel)
+        self._ext_block_q = self._extend_block_q      # block_q of the current forward's plan
         self.num_draft_tokens = _spec_num_draft_tokens(model_runner)
         self.forward_metadata = None
         #: optional (start, stop) torch.cuda.Event pair re-recorded around the next decode attention kernel
@@ -238,6 +244,7 @@ class B200AttnBackend(_Base):
         if mode.is_target_verify():
             # every request extends by draft_token_num tokens over `seq_lens` cached ones (triton_backend.py:807-866)
             n = self._spec_tokens_per_req(forward_batch)
+            self._ext_block_q = self._pick_block_q(n)
             mask = getattr(spec, "custom_mask", None)
             st = self._select_ext((int(mode), bs), bs, bs * n, 0 if mask is None else int(mask.numel()), in_capture)
             pre = forward_batch.seq_lens[:bs]
@@ -257,6 +264,7 @@ class B200AttnBackend(_Base):
             # CUDA-graph draft-extend: a fixed number of query rows per request; the cached prefix is
             # seq_lens - accepted tokens, clamped for padded rows (triton_backend.py:529-565)
             n = self._spec_tokens_per_req(forward_batch)
+            self._ext_block_q = self._pick_block_q(n)
             st = self._select_ext((int(mode), bs), bs, bs * n, 0, in_capture)
             seq = forward_batch.seq_lens[:bs]
             ext = st.ext_lens(seq.dtype)[:bs]
@@ -274,6 +282,8 @@ class B200AttnBackend(_Base):
             T = getattr(forward_batch, "extend_num_tokens", None)
             if T is None:
                 T = forward_batch.out_cache_loc.shape[0]
+            lens_cpu = getattr(forward_batch, "extend_seq_lens_cpu", None)      # host copy the scheduler keeps
+            self._ext_block_q = self._pick_block_q(max(lens_cpu) if lens_cpu is not None and len(lens_cpu) else None)
             self._ext = self._select_ext((int(mode), bs), bs, int(T), 0, in_capture)
             self._ext_lens = (forward_batch.extend_prefix_lens, forward_batch.extend_seq_lens, None, None)
 
@@ -294,11 +304,18 @@ class B200AttnBackend(_Base):
             # page_size >= 16: the plan also verifies that pages are runs of consecutive pool rows (the paged
             # allocator's layout), which lets forward_extend fetch K/V by TMA page boxes
             paged = self.page_size >= 16 and pre is not None and pre.dtype == ext.dtype
-            ops.extend_plan(self._ext.ws, ext, self._extend_block_q,
+            ops.extend_plan(self._ext.ws, ext, self._ext_block_q,
                             page_size=self.page_size if paged else 1,
                             req_to_token=self.req_to_token_pool.req_to_token if paged else None,
                             req_pool_indices=forward_batch.req_pool_indices[: ext.shape[0]] if paged else None,
                             extend_prefix_lens=pre if paged else None)
+
+    def _pick_block_q(self, max_extend_len) -> int:
+        """Query tokens per work item for this forward: one-tile items when the host knows that no request extends
+        by more than one tile's worth of tokens (every request then is exactly one item), else two-tile items."""
+        if self._one_tile_block_q and max_extend_len is not None and 0 < int(max_extend_len) <= self._one_tile_block_q:
+            return self._one_tile_block_q
+        return self._extend_block_q
 
     # ------------------------------------------------------------------ CUDA graphs
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):

@@ -154,11 +154,18 @@ __device__ __forceinline__ uint32_t swz_off(int row, int chunk, int rows) {
 // exp-bound rather than MMA-bound.)
 // kTma: the K/V ring may be filled by TMA page boxes through the two tensor maps (16-bit pools, page_size >= 16);
 // the instance also carries the row-gather producer and picks per launch from the plan's page check.
-template <typename QT, int kEmu, bool kFp8, bool kOpts, int kHD, bool kTma>
+// kOneTile: ONE query tile of 128 rows per work item (the plan was built with block_q = 128 / group) -- the instance
+// for short extends (TARGET_VERIFY / DRAFT_EXTEND, a few new tokens after a long cached prefix), where the second
+// tile of the two-tile kernel would be empty.  The two S regions of TMEM then double-buffer the SAME tile across kv
+// blocks: QK(j+2) is issued right behind PV(j), so S(j+1) is already waiting when the softmax warps finish block j
+// and the tile's chain is the softmax pass alone instead of softmax + MMAs.  Valid for any extend length.
+template <typename QT, int kEmu, bool kFp8, bool kOpts, int kHD, bool kTma, bool kOneTile>
 __global__ void __launch_bounds__(tc::kThreads, 1)
 extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constant__ CUtensorMap tm_k,
                  const __grid_constant__ CUtensorMap tm_v) {
   static_assert(!(kTma && kFp8), "the FP8 producers widen bytes themselves");
+  static_assert(!(kTma && kOneTile), "the one-tile instance keeps the row gather");
+  constexpr int kNT = kOneTile ? 1 : tc::kQTiles;           // query tiles of this instance
   using namespace tc;
   using namespace ptx;
   using L = Layout<kFp8>;
@@ -187,7 +194,7 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
   const int E = (int)load_index(p.extend_seq_lens, p.lens_is_i64, req);
   const int64_t pool_row = load_index(p.req_pool_indices, p.req_pool_indices_is_i64, req);
   const int q_tok0 = qo_indptr[req] + q_start;            // first global q row of this item
-  const int n_q = min(kQTiles * BQ, E - q_start);          // valid query tokens in this item
+  const int n_q = min(kNT * BQ, E - q_start);              // valid query tokens in this item
   // a custom (tree) mask replaces the causal rule on the new tokens: every row may see all P + E positions
   const bool masked = kOpts && p.custom_mask != nullptr;
   const int kv_end = (p.causal && !masked) ? P + q_start + n_q : P + E;   // kv positions [kv_off, kv_end) are needed
@@ -208,7 +215,7 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
       mbar_init(bar(kBarFull + s), use_tma ? 1 : kProducerThreads);
       mbar_init(bar(kBarEmpty + s), 1);
     }
-    for (int t = 0; t < kQTiles; ++t) {
+    for (int t = 0; t < kQTiles; ++t) {                   // (one-tile instance: S buffer t; ODone + 1 = "PV done")
       mbar_init(bar(kBarSFull + t), 1);
       mbar_init(bar(kBarPFull + t), kSoftmaxWarps);
       mbar_init(bar(kBarODone + t), 1);
@@ -261,6 +268,8 @@ bool extend_fast_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype
 
 // query tokens per work item (two 128-row tiles of 128/group tokens each)
 int extend_fast_block_q(int group) { return tc::kQTiles * (128 / group); }
+// ... or one 128-row tile (the kOneTile instance): the host picks it when no request extends by more tokens
+int extend_fast_block_q_one_tile(int group) { return 128 / group; }
 
 bool extend_fast_layout_ok(const ExtendParams& p, int kv_dtype) {
   const int kv_align = (kv_dtype == B200_FP8_E4M3 || kv_dtype == B200_FP8_E5M2) ? 16 : 8;   // 16-byte pieces
@@ -320,13 +329,13 @@ bool extend_tma_ok(const ExtendParams& p, const b200_extend_args& a) {
          p.k_stride_s >= (int64_t)p.num_kv_heads * p.head_dim_qk && p.v_stride_s >= (int64_t)p.num_kv_heads * p.head_dim_v;
 }
 
-template <typename QT, bool kFp8, bool kOpts, int kHD, bool kTma>
+template <typename QT, bool kFp8, bool kOpts, int kHD, bool kTma, bool kOneTile = false>
 int launch_extend_fast_t(const ExtendParams& p_in, const b200_extend_args& a, cudaStream_t stream) {
   ExtendParams p = p_in;
   p.tma_rows = kTma ? extend_tma_rows(a.page_size) : 0;
   static std::atomic<uint64_t> configured{0};
   constexpr int kSmem = tc::Layout<kFp8>::kSmemBytes;
-  auto kern = extend_tc_kernel<QT, tc::kEmuEighths, kFp8, kOpts, kHD, kTma>;
+  auto kern = extend_tc_kernel<QT, tc::kEmuEighths, kFp8, kOpts, kHD, kTma, kOneTile>;
   B200_CHECK_CUDA(set_max_dynamic_smem(kern, kSmem, configured));
   CUtensorMap tm_k, tm_v;
   memset(&tm_k, 0, sizeof(tm_k));
@@ -341,7 +350,7 @@ int launch_extend_fast_t(const ExtendParams& p_in, const b200_extend_args& a, cu
       return B200_ECUDA;
     }
   }
-  const int block_q = extend_fast_block_q(p.group);
+  const int block_q = kOneTile ? extend_fast_block_q_one_tile(p.group) : extend_fast_block_q(p.group);
   // host-side bound on the number of work items: sum_r ceil(E_r / block_q) <= T / block_q + bs
   int64_t tiles = a.num_q_tokens / block_q + a.batch_size;
   if (tiles > a.max_tiles) tiles = a.max_tiles;
@@ -355,6 +364,9 @@ int launch_extend_fast_t(const ExtendParams& p_in, const b200_extend_args& a, cu
 template <typename QT, bool kFp8, int kHD>
 int launch_extend_fast_d(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr || p.custom_mask != nullptr;
+  if (a.block_q == extend_fast_block_q_one_tile(p.group))          // the plan holds one-tile items
+    return opts ? launch_extend_fast_t<QT, kFp8, true, kHD, false, true>(p, a, stream)
+                : launch_extend_fast_t<QT, kFp8, false, kHD, false, true>(p, a, stream);
   if constexpr (!kFp8) {
     if (extend_tma_ok(p, a))      // page_size >= 16: TMA page boxes; page_size 1 keeps the LDGSTS gather
       return opts ? launch_extend_fast_t<QT, false, true, kHD, true>(p, a, stream)
@@ -374,7 +386,9 @@ int launch_extend_fast(const ExtendParams& p, const b200_extend_args& a, cudaStr
   const bool fp8 = a.kv_dtype == B200_FP8_E4M3 || a.kv_dtype == B200_FP8_E5M2;
   const int bq1 = extend_fast_block_q(p.group);
   const int bq = a.block_q > 0 ? a.block_q : bq1;
-  B200_CHECK_ARG(bq == bq1, "extend: the plan was built with block_q %d, the tcgen05 kernel needs %d", bq, bq1);
+  B200_CHECK_ARG(bq == bq1 || bq == extend_fast_block_q_one_tile(p.group),
+                 "extend: the plan was built with block_q %d, the tcgen05 kernel needs %d (or %d: one-tile items)", bq, bq1,
+                 extend_fast_block_q_one_tile(p.group));
   if (a.q_dtype == B200_BF16)
     return fp8 ? launch_extend_fast_q<__nv_bfloat16, true>(p, a, stream)
                : launch_extend_fast_q<__nv_bfloat16, false>(p, a, stream);

@@ -367,6 +367,15 @@ def extend_block_q(head_dim_qk: int, head_dim_v: int, group: int, q_dtype, kv_dt
                                               dtype_code(kv_dtype), kernel))
 
 
+def extend_block_q_one_tile(head_dim_qk: int, head_dim_v: int, group: int, q_dtype, kv_dtype,
+                             kernel: int = KERNEL_AUTO) -> int:
+    """block_q of the tcgen05 kernel's one-tile instance (128 / group tokens per work item; pass it to `extend_plan`
+    when no request extends by more than that many tokens), or 0 when the generic kernel will run."""
+    if kernel == KERNEL_GENERIC or not extend_fast_supported(head_dim_qk, head_dim_v, group, q_dtype, kv_dtype):
+        return 0
+    return extend_block_q(head_dim_qk, head_dim_v, group, q_dtype, kv_dtype, kernel) // 2
+
+
 def extend_fast_supported(head_dim_qk: int, head_dim_v: int, group: int, q_dtype, kv_dtype) -> bool:
     return bool(_C.lib.b200attn_extend_fast_supported(head_dim_qk, head_dim_v, group, dtype_code(q_dtype),
                                                       dtype_code(kv_dtype)))

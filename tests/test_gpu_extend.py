@@ -55,13 +55,16 @@ def make_extend_problem(Hq, Hkv, D, prefix, extend, page_size, dtype, pool_dtype
 
 
 def run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, kernel=0, causal=True, want_lse=False,
-                   page_size=1):
+                   page_size=1, one_tile=False):
     from sglang_b200 import ops
 
     sm, _, _ = ops.device_info()
     T, Hq, D = q.shape
     group = Hq // kp.shape[1]
     bq = ops.extend_block_q(D, D, group, q.dtype, pool_dtype, kernel)
+    if one_tile:                     # the tcgen05 kernel's one-tile instance (valid for any extend length)
+        bq = ops.extend_block_q_one_tile(D, D, group, q.dtype, pool_dtype, kernel)
+        assert bq > 0
     ws = ops.ExtendWorkspace.create(len(pre), T // bq + len(pre) + 1, "cuda", num_ctas=sm)
     ext_g, pre_g = ext.cuda(), pre.cuda()
     rtt_g, rpi_g = rtt.cuda(), rpi.cuda()
@@ -93,6 +96,29 @@ SHAPES = [
     (8, 2, 128, [100, 700], [513, 20], 256),
     (8, 2, 64, [31, 500], [200, 77], 32),
 ]
+
+
+@pytest.mark.parametrize("dtype,pool_dtype", [(torch.bfloat16, torch.bfloat16), (torch.float16, torch.float16),
+                                              (torch.bfloat16, torch.float8_e4m3fn), (torch.float16, torch.float8_e5m2)])
+@pytest.mark.parametrize("shape", SHAPES, ids=[f"h{s[0]}_{s[1]}_d{s[2]}_p{s[5]}" for s in SHAPES])
+def test_extend_one_tile_instance_vs_oracle(shape, dtype, pool_dtype):
+    """The one-tile instance (S double-buffered across kv blocks; the backend picks it for short extends) on every
+    shape the tcgen05 kernel covers, incl. multi-tile requests, and bit-compared with the two-tile instance's LSE
+    within float tolerance."""
+    from sglang_b200 import ops
+
+    Hq, Hkv, D, prefix, extend, page = shape
+    if not ops.extend_fast_supported(D, D, Hq // Hkv, dtype, pool_dtype):
+        pytest.skip("generic kernel shape")
+    q, kp, vp, rtt, rpi, pre, ext = make_extend_problem(Hq, Hkv, D, prefix, extend, page, dtype, pool_dtype, seed=D + 1)
+    scale = D**-0.5
+    got, lse1 = run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, page_size=page, one_tile=True,
+                               want_lse=True)
+    want = ref.extend_ref(q, kp, vp, rtt, rpi, pre, ext, scale, kv_dtype=pool_dtype)
+    assert_close_scaled(got, want)
+    got2, lse2 = run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, page_size=page, want_lse=True)
+    assert float((lse1 - lse2).abs().max()) <= 2e-3
+    assert float((got - got2).abs().max()) <= 2e-2
 
 
 @pytest.mark.parametrize("kernel", list(KERNELS))

@@ -343,6 +343,7 @@ def test_backend_target_verify_and_lse():
                       seq_lens=torch.tensor(prefix, dtype=torch.int32, device="cuda"), out_cache_loc=pb.loc.cuda(),
                       seq_lens_sum=sum(prefix), spec_info=spec, mha_return_lse=True)
     pb.backend.init_forward_metadata(fb)
+    assert pb.backend.extend_ws.block_q == 128 // (Hq // Hkv)      # 8 draft tokens per request: one-tile items
     layer = RadixAttention(Hq, D, D ** -0.5, Hkv, 0)
     out, lse = layer(pb.q.cuda().reshape(pb.T, -1), pb.k_new.cuda().reshape(pb.T, -1),
                      pb.v_new.cuda().reshape(pb.T, -1), fb, pb.backend)
