@@ -248,6 +248,10 @@ def main():
         emit(extend_case("cfg5/16 with one-tile items (for reference)", 8, 16384, 1024, 32, 8, 128, it, one_tile=True))
         emit(extend_case("verify 64 req x (4K + 8 draft, tree mask), generic", 64, 4096, 8, 32, 8, 128, 3,
                          shared=False, tree_mask=True, kernel=1))
+        emit(extend_case("D256 gemma-2 heads (16/8) 8 req x (16K shared prefix + 1K), tcgen05 one-tile", 8, 16384, 1024, 16, 8,
+                         256, it))
+        emit(extend_case("D256 gemma-2 heads (16/8), generic kernel (CUDA cores), 1 req x (4K + 256)", 1, 4096, 256, 16, 8,
+                         256, 3, kernel=1))
         emit(extend_case("D64 qwen2.5-0.5b heads 8 req x (16K shared prefix + 1K)", 8, 16384, 1024, 14, 2, 64, it))
         emit(extend_case("D64 32/8 heads 8 req x (16K shared prefix + 1K)", 8, 16384, 1024, 32, 8, 64, it))
         emit(extend_case("D64 32/8 heads, generic kernel (CUDA cores), 2 req", 2, 16384, 1024, 32, 8, 64, 3, kernel=1))

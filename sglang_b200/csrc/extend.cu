@@ -277,7 +277,7 @@ extern "C" int b200attn_extend_fast_supported(int32_t dqk, int32_t dv, int32_t g
 extern "C" int b200attn_extend_block_q(int32_t dqk, int32_t dv, int32_t group, int32_t q_dtype,
                                        int32_t kv_dtype, int32_t kernel) {
   if (kernel != B200_KERNEL_GENERIC && b200::extend_fast_supported(dqk, dv, group, q_dtype, kv_dtype))
-    return b200::extend_fast_block_q(group);
+    return b200::extend_fast_block_q(group, dqk);
   return 64;  // the generic kernel ignores tiles; any value gives a valid plan
 }
 

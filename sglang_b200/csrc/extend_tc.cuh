@@ -165,9 +165,16 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
                  const __grid_constant__ CUtensorMap tm_v) {
   static_assert(!(kTma && kFp8), "the FP8 producers widen bytes themselves");
   static_assert(!(kTma && kOneTile), "the one-tile instance keeps the row gather");
+  static_assert(kHD != 256 || (kOneTile && !kFp8), "D = 256 exists as the one-tile, 16-bit-pool instance only");
   constexpr int kNT = kOneTile ? 1 : tc::kQTiles;           // query tiles of this instance
   using namespace tc;
   using namespace ptx;
+  // Tile geometry of this instance (these shadow tc::).  D = 256: rows are 512 bytes = four 64-wide d groups, a kv
+  // block is 64 rows so that K_j (or V_j) still fills one 32 KiB ring slot, the Q tile takes both Q areas (64 KiB),
+  // S is 128 x 64 and O takes both O regions of TMEM (256 columns): S0 S1 O = 512 columns.
+  constexpr int kBlockKV = kHD == 256 ? 64 : tc::kBlockKV;  // kv rows per block
+  constexpr int kHalfBytes = kBlockKV * 128;                // distance between the 64-wide d groups of a K/V tile
+  constexpr int kQHalfBytes = 128 * 128;                    // ... of a Q tile (always 128 rows)
   using L = Layout<kFp8>;
   using CT = typename std::conditional<kFp8, __half, QT>::type;   // MMA operand type
   constexpr int kSlots = L::kSlots, kSmemQ = L::kSmemQ, kSmemKV = L::kSmemKV, kSmemRaw = L::kSmemRaw,
@@ -260,14 +267,15 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
 
 
 bool extend_fast_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype) {
-  if (dqk != dv || (dqk != 128 && dqk != 64)) return false;
+  if (dqk != dv || (dqk != 128 && dqk != 64 && dqk != 256)) return false;
   if (group < 1 || group > 128) return false;
   if (q_dtype != B200_BF16 && q_dtype != B200_F16) return false;
+  if (dqk == 256) return kv_dtype == q_dtype;          // D = 256: 16-bit pools (one-tile instance)
   return kv_dtype == q_dtype || kv_dtype == B200_FP8_E4M3 || kv_dtype == B200_FP8_E5M2;
 }
 
-// query tokens per work item (two 128-row tiles of 128/group tokens each)
-int extend_fast_block_q(int group) { return tc::kQTiles * (128 / group); }
+// query tokens per work item (two 128-row tiles of 128/group tokens each; D = 256 has the one-tile instance only)
+int extend_fast_block_q(int group, int head_dim) { return (head_dim == 256 ? 1 : tc::kQTiles) * (128 / group); }
 // ... or one 128-row tile (the kOneTile instance): the host picks it when no request extends by more tokens
 int extend_fast_block_q_one_tile(int group) { return 128 / group; }
 
@@ -350,7 +358,7 @@ int launch_extend_fast_t(const ExtendParams& p_in, const b200_extend_args& a, cu
       return B200_ECUDA;
     }
   }
-  const int block_q = kOneTile ? extend_fast_block_q_one_tile(p.group) : extend_fast_block_q(p.group);
+  const int block_q = kOneTile ? extend_fast_block_q_one_tile(p.group) : extend_fast_block_q(p.group, kHD);
   // host-side bound on the number of work items: sum_r ceil(E_r / block_q) <= T / block_q + bs
   int64_t tiles = a.num_q_tokens / block_q + a.batch_size;
   if (tiles > a.max_tiles) tiles = a.max_tiles;
@@ -378,13 +386,20 @@ int launch_extend_fast_d(const ExtendParams& p, const b200_extend_args& a, cudaS
 
 template <typename QT, bool kFp8>
 int launch_extend_fast_q(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
+  if constexpr (!kFp8) {
+    if (p.head_dim_qk == 256) {
+      const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr || p.custom_mask != nullptr;
+      return opts ? launch_extend_fast_t<QT, false, true, 256, false, true>(p, a, stream)
+                  : launch_extend_fast_t<QT, false, false, 256, false, true>(p, a, stream);
+    }
+  }
   return p.head_dim_qk == 64 ? launch_extend_fast_d<QT, kFp8, 64>(p, a, stream)
                              : launch_extend_fast_d<QT, kFp8, 128>(p, a, stream);
 }
 
 int launch_extend_fast(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   const bool fp8 = a.kv_dtype == B200_FP8_E4M3 || a.kv_dtype == B200_FP8_E5M2;
-  const int bq1 = extend_fast_block_q(p.group);
+  const int bq1 = extend_fast_block_q(p.group, p.head_dim_qk);
   const int bq = a.block_q > 0 ? a.block_q : bq1;
   B200_CHECK_ARG(bq == bq1 || bq == extend_fast_block_q_one_tile(p.group),
                  "extend: the plan was built with block_q %d, the tcgen05 kernel needs %d (or %d: one-tile items)", bq, bq1,

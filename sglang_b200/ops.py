@@ -373,7 +373,7 @@ def extend_block_q_one_tile(head_dim_qk: int, head_dim_v: int, group: int, q_dty
     when no request extends by more than that many tokens), or 0 when the generic kernel will run."""
     if kernel == KERNEL_GENERIC or not extend_fast_supported(head_dim_qk, head_dim_v, group, q_dtype, kv_dtype):
         return 0
-    return extend_block_q(head_dim_qk, head_dim_v, group, q_dtype, kv_dtype, kernel) // 2
+    return 128 // group
 
 
 def extend_fast_supported(head_dim_qk: int, head_dim_v: int, group: int, q_dtype, kv_dtype) -> bool:
