@@ -394,6 +394,8 @@ def main():
                                       ours_only=oo))
         emit(extend_compare_blackwell("cfg5 128 req x (16K shared prefix + 1K), page 64", 128, 16384, 1024, 32, 8,
                                       128, 64, iters=3, ours_only=oo))
+        emit(extend_compare_blackwell("D256 gemma-2 heads (16/8) 8 req x (16K shared prefix + 1K), page 64", 8, 16384,
+                                      1024, 16, 8, 256, 64, ours_only=oo))
     if args.only in (None, "triton"):
         emit(decode_compare_triton("cfg2 8B bf16 bs64 ctx4096 page1", 64, 4096, 32, 8, 128))
         emit(decode_compare_triton("cfg4 70B tp8 bs32 ctx32768 page1", 32, 32768, 8, 1, 128))
