@@ -10,7 +10,12 @@ from sweep import extend_case
 from sglang_b200 import _C
 
 page = int(sys.argv[1]) if len(sys.argv) > 1 else 1
-print(extend_case("trace 8 req x (16K + 1K)", 8, 16384, 1024, 32, 8, 128, 3, page=page))
+D = int(sys.argv[2]) if len(sys.argv) > 2 else 128           # 256: the one-tile D 256 instance (Gemma-2 heads)
+one_tile = len(sys.argv) > 3 and sys.argv[3] == "one"
+if D == 256:
+    print(extend_case("trace D256 8 req x (16K + 1K)", 8, 16384, 1024, 16, 8, 256, 3, page=page))
+else:
+    print(extend_case("trace 8 req x (16K + 1K)", 8, 16384, 1024, 32, 8, 128, 3, page=page, one_tile=one_tile))
 torch.cuda.synchronize()
 buf = np.zeros(16 * 512, dtype=np.int64)
 rc = _C.lib.b200attn_dev_trace_read(buf.ctypes.data_as(ctypes.c_void_p))

@@ -74,6 +74,9 @@ __device__ long long g_ext_trace[16 * 512];
 #ifndef B200_EMU
 #define B200_EMU 4      // sixteenths of the column pairs that take the polynomial exp2
 #endif
+#ifndef B200_RING_FENCE
+#define B200_RING_FENCE 1   // fence.proxy.async in the MMA warp after every ring-slot wait (A/B switch of dev builds)
+#endif
 #ifndef B200_EMU_ALT
 #define B200_EMU_ALT 1      // spread them over the row instead of taking the first ones of every 16
 #endif
