@@ -275,7 +275,32 @@ def _backend_problem(Hq, Hkv, D, prefix, new_lens, *, sliding_window=None, seed=
                            q=q, k_new=k_new, v_new=v_new, loc=loc, kp=kp, vp=vp, lens=lens, bs=bs, T=T)
 
 
-@pytest.mark.parametrize("Hq,Hkv,D", [(32, 8, 128), (64, 8, 64), (8, 2, 128)])
+def test_backend_short_extend_plans_one_tile_items():
+    """A few new tokens behind cached prefixes (multi-turn chat): the scheduler's host copy of the extend lengths tells
+    the backend that one 128-row tile per request is enough; a longer request in the batch switches back."""
+    from sglang_b200.srt_mirror import ForwardBatch, ForwardMode, RadixAttention
+
+    Hq, Hkv, D = 32, 8, 128
+    layer = RadixAttention(Hq, D, D ** -0.5, Hkv, 0)
+    for prefix, ext, want_bq in (([900, 0, 130], [17, 32, 1], 32), ([900, 0, 130], [17, 33, 1], 64)):
+        pb = _backend_problem(Hq, Hkv, D, prefix, ext, seed=sum(ext))
+        fb = ForwardBatch(forward_mode=ForwardMode.EXTEND, batch_size=pb.bs, req_pool_indices=pb.rpi.cuda(),
+                          seq_lens=torch.tensor(pb.lens, dtype=torch.int32, device="cuda"), out_cache_loc=pb.loc.cuda(),
+                          seq_lens_sum=sum(pb.lens),
+                          extend_prefix_lens=torch.tensor(prefix, dtype=torch.int32, device="cuda"),
+                          extend_seq_lens=torch.tensor(ext, dtype=torch.int32, device="cuda"),
+                          extend_prefix_lens_cpu=prefix, extend_seq_lens_cpu=ext, extend_num_tokens=sum(ext))
+        pb.backend.init_forward_metadata(fb)
+        assert pb.backend.extend_ws.block_q == want_bq
+        out = layer(pb.q.cuda().reshape(pb.T, -1), pb.k_new.cuda().reshape(pb.T, -1), pb.v_new.cuda().reshape(pb.T, -1),
+                    fb, pb.backend)
+        torch.cuda.synchronize()
+        want = ref.extend_ref(pb.q, pb.kp, pb.vp, pb.rtt, pb.rpi, torch.tensor(prefix, dtype=torch.int32),
+                              torch.tensor(ext, dtype=torch.int32), D ** -0.5)
+        assert_close_scaled(out.float().cpu().view_as(want), want, f"extend lens {ext}")
+
+
+@pytest.mark.parametrize("Hq,Hkv,D", [(32, 8, 128), (64, 8, 64), (8, 2, 128), (16, 8, 256)])
 def test_backend_hybrid_sliding_window(Hq, Hkv, D):
     """A hybrid model: layer 0 sliding window (W = 127 -> 128 keys) with sinks, layer 1 full attention; decode and
     extend through the plugin API, one metadata call per forward (two decode plans)."""
