@@ -20,6 +20,8 @@
  *   b200attn_decode          srt/layers/attention/torch_native_backend.py:176-277 (oracle semantics),
  *                            kernels/ops/attention/decode_attention.py:968-1044 (decode_attention_fwd:
  *                            split-KV stage 1 + stage-2 merge)
+ *   b200attn_decode_static_ws  none: no counterpart in the reference, added
+ *                            (b200attn_decode with the split workspace in a static device array; see below)
  *   b200attn_extend_plan     srt/layers/attention/triton_backend.py:860-900 (qo_indptr / kv_indptr for extend)
  *   b200attn_rope_store_kv   srt/layers/rotary_embedding/base.py:234-275,363-385 + set_kv_buffer (see below)
  *   b200attn_extend          srt/layers/attention/torch_native_backend.py:61-174 (oracle semantics),
@@ -176,6 +178,27 @@ typedef struct b200_decode_args {
 } b200_decode_args;
 
 int b200attn_decode(const b200_decode_args* args, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------ *
+ * b200attn_decode without a caller-owned split-KV workspace.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments, same kernels and same results as b200attn_decode,
+ * except that args->ws_o / args->ws_lse are IGNORED (may be NULL): the split partials live in a file-scope
+ * `static __device__` array of B200_DECODE_STATIC_WS_BYTES inside the library (decode.cu), which every GPU that
+ * loads the library holds until exit.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library
+ * routine); inputs, outputs and the plan stay caller-owned.
+ *   limit   max_chunks * Hq * Dv floats (rounded up to 64) + max_chunks * Hq floats <= B200_DECODE_STATIC_WS_BYTES / 4;
+ *           beyond it the call returns B200_EINVAL and b200attn_last_error() names both sizes.  Choose max_chunks
+ *           (the plan capacity) accordingly, e.g. Hq 32, Dv 128: max_chunks <= 1 016.
+ *   set-up  the first call on a device resolves the array's device address (cudaGetSymbolAddress, cached per
+ *           device); make that first call with the device current and outside stream capture.
+ *   sharing every call on a device uses the SAME array, and it keeps the last call's partials.  Nothing in it has to
+ *           start at zero (each launch writes every partial it later reads), so nothing is cleared -- but two
+ *           calls that overlap on the GPU (different streams, or graphs replayed concurrently) race on it.
+ * ------------------------------------------------------------------------ */
+#define B200_DECODE_STATIC_WS_BYTES (16 * 1024 * 1024)
+int b200attn_decode_static_ws(const b200_decode_args* args, b200_stream_t stream);
+
 /* 1 if the fast (mma) decode kernel covers this shape, else 0 */
 int b200attn_decode_fast_supported(int32_t head_dim_qk, int32_t head_dim_v, int32_t group,
                                    int32_t q_dtype, int32_t kv_dtype);

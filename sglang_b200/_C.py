@@ -134,6 +134,7 @@ SYMBOLS = {
     "b200attn_rope_store_kv": (C.c_int, [C.POINTER(RopeStoreArgs), vp]),
     "b200attn_decode_plan": (C.c_int, [C.POINTER(DecodePlanArgs), vp]),
     "b200attn_decode": (C.c_int, [C.POINTER(DecodeArgs), vp]),
+    "b200attn_decode_static_ws": (C.c_int, [C.POINTER(DecodeArgs), vp]),
     "b200attn_decode_fast_supported": (C.c_int, [i32] * 5),
     "b200attn_decode_ctas_per_sm": (C.c_int, [i32, i32]),
     "b200attn_decode_items_per_chunk": (C.c_int, [i32] * 6),

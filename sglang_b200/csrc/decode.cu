@@ -514,3 +514,64 @@ extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_)
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// b200attn_decode_static_ws: b200attn_decode for callers that cannot allocate (no counterpart in the reference).
+// The split-KV partials go to a file-scope device array instead of
+// caller memory.  `g_decode_static_ws` is a HOST-SIDE STAND-IN in host code, not a device address: the address the
+// kernels get comes from cudaGetSymbolAddress, resolved once per device with that device current.
+// Every call on a device shares the array (overlapping calls race); nothing in it has to start at zero, because
+// each launch writes every (chunk, head) partial its merge reads.
+// ---------------------------------------------------------------------------------------------------------------
+namespace b200 {
+namespace {
+constexpr int64_t kStaticWsFloats = (int64_t)B200_DECODE_STATIC_WS_BYTES / (int64_t)sizeof(float);
+static __device__ __align__(256) float g_decode_static_ws[kStaticWsFloats];
+
+constexpr int kStaticWsMaxDevices = 64;
+std::atomic<float*> g_static_ws_addr[kStaticWsMaxDevices];
+
+// device address of the array on the CURRENT device (set-up on first use, no allocation)
+int static_ws_address(float** out) {
+  int dev = -1;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_CHECK_ARG(dev >= 0 && dev < kStaticWsMaxDevices, "decode_static_ws: device ordinal %d >= %d", dev,
+                 kStaticWsMaxDevices);
+  float* ptr = g_static_ws_addr[dev].load(std::memory_order_acquire);
+  if (ptr == nullptr) {
+    void* sym = nullptr;
+    B200_CHECK_CUDA(cudaGetSymbolAddress(&sym, g_decode_static_ws));
+    B200_CHECK_ARG(sym != nullptr, "decode_static_ws: cudaGetSymbolAddress returned null on device %d", dev);
+    ptr = static_cast<float*>(sym);
+    g_static_ws_addr[dev].store(ptr, std::memory_order_release);
+  }
+  *out = ptr;
+  return B200_OK;
+}
+}  // namespace
+}  // namespace b200
+
+extern "C" int b200attn_decode_static_ws(const b200_decode_args* a, b200_stream_t stream_) {
+  using namespace b200;
+  B200_CHECK_ARG(a != nullptr, "decode_static_ws: null args");
+  if (a->batch_size == 0) return B200_OK;
+  B200_CHECK_ARG(a->max_chunks > 0 && a->num_q_heads > 0 && a->head_dim_v > 0,
+                 "decode_static_ws: max_chunks %d, Hq %d, Dv %d must be positive", a->max_chunks, a->num_q_heads,
+                 a->head_dim_v);
+  // ws_o first (rounded up so that ws_lse starts 256-byte aligned), then ws_lse
+  const int64_t o_floats = ((int64_t)a->max_chunks * a->num_q_heads * a->head_dim_v + 63) / 64 * 64;
+  const int64_t lse_floats = (int64_t)a->max_chunks * a->num_q_heads;
+  B200_CHECK_ARG(o_floats + lse_floats <= kStaticWsFloats,
+                 "decode_static_ws: max_chunks %d x Hq %d x (Dv %d + 1) needs %lld bytes of split workspace, the "
+                 "static array holds %lld (B200_DECODE_STATIC_WS_BYTES); plan with fewer chunks or use "
+                 "b200attn_decode with caller memory",
+                 a->max_chunks, a->num_q_heads, a->head_dim_v, (long long)((o_floats + lse_floats) * 4),
+                 (long long)B200_DECODE_STATIC_WS_BYTES);
+  float* ws = nullptr;
+  const int rc = static_ws_address(&ws);
+  if (rc != B200_OK) return rc;
+  b200_decode_args b = *a;
+  b.ws_o = ws;
+  b.ws_lse = ws + o_floats;
+  return b200attn_decode(&b, stream_);
+}
