@@ -54,7 +54,7 @@ def time_cuda_graph(fn, reps=20, iters=10):
     return time_cuda(g.replay, iters, warmup=2) / reps
 
 
-def decode_case(name, bs, L, Hq, Hkv, D, pool_dtype, page, iters, ragged=False):
+def decode_case(name, bs, L, Hq, Hkv, D, pool_dtype, page, iters, ragged=False, kernel=0):
     dev = "cuda"
     g = torch.Generator(device=dev).manual_seed(0)
     lens = torch.full((bs,), L, dtype=torch.int32, device=dev)
@@ -79,7 +79,7 @@ def decode_case(name, bs, L, Hq, Hkv, D, pool_dtype, page, iters, ragged=False):
     ops.decode_plan(ws, lens, Hkv, items_per_chunk=ops.decode_items_per_chunk(Hq, Hkv, D, D, torch.bfloat16, pool_dtype))
 
     def fn():
-        ops.decode_attention(q, o, kp, vp, rtt, rpi, lens, ws, D**-0.5, kv_dtype=pool_dtype)
+        ops.decode_attention(q, o, kp, vp, rtt, rpi, lens, ws, D**-0.5, kv_dtype=pool_dtype, kernel=kernel)
 
     t_eager = time_cuda(fn, iters)
     t, timing = t_eager, "eager"
@@ -218,6 +218,14 @@ def main():
                 emit(decode_case(f"cfg4 70B tp{tp} bs{bs} ctx32768", bs, 32768, hq, hkv, 128, bf, 1, a.iters))
         emit(decode_case("cfg4 70B tp8 fp8 bs32 ctx32768", 32, 32768, 8, 1, 128, e4, 1, a.iters))
         emit(decode_case("small bs1 ctx4096 8B", 1, 4096, 32, 8, 128, bf, 1, a.iters))
+    if a.only in ("", "decode", "d64"):
+        # D = 64 heads (gpt-oss 64/8, Llama-3.2-1B 32/8): bf16 pool, FP8 pool on the head-group kernel, and the
+        # CUDA-core kernel FP8 pools of this head dim took before
+        emit(decode_case("D64 gpt-oss heads 64/8 bf16 bs64 ctx8192", 64, 8192, 64, 8, 64, bf, 1, a.iters))
+        emit(decode_case("D64 gpt-oss heads 64/8 fp8 bs64 ctx8192", 64, 8192, 64, 8, 64, e4, 1, a.iters))
+        emit(decode_case("D64 gpt-oss heads 64/8 fp8 bs64 ctx8192, generic kernel", 64, 8192, 64, 8, 64, e4, 1,
+                         max(3, a.iters // 10), kernel=1))
+        emit(decode_case("D64 llama-3.2-1b heads 32/8 fp8 bs128 ctx8192 page16", 128, 8192, 32, 8, 64, e4, 16, a.iters))
     if a.only in ("", "store"):
         emit(store_case("decode store 64 rows 8B bf16", 64, 8, 128, bf, a.iters))
         emit(store_case("decode store 256 rows 8B fp8", 256, 8, 128, e4, a.iters))

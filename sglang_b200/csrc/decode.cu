@@ -430,7 +430,7 @@ bool decode_hg_enabled() {
 }
 bool decode_hg_shape_ok(int hq, int hkv, int dqk, int dv, int q_dtype, int kv_dtype) {
   if (!decode_hg_enabled() || hkv <= 0 || hq % hkv != 0 || hkv % kHG != 0) return false;
-  if (!decode_fast_supported(dqk, dv, hq / hkv, q_dtype, kv_dtype)) return false;
+  if (!decode_hg_dims_supported(dqk, dv, hq / hkv, q_dtype, kv_dtype)) return false;
   return !(dqk == 256 && kv_dtype != B200_FP8_E4M3);
 }
 }  // namespace
@@ -483,15 +483,18 @@ extern "C" int b200attn_decode(const b200_decode_args* a, b200_stream_t stream_)
   p.sm_scale = a->sm_scale; p.k_scale = a->k_scale; p.v_scale = a->v_scale; p.logit_cap = a->logit_cap;
   p.window_keys = a->window_keys > 0 ? a->window_keys : 0; p.sinks = a->sinks; p.lse = a->lse;
 
-  const bool fast_ok = decode_fast_supported(a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype) &&
-                       decode_fast_layout_ok(p, a->kv_dtype);
+  // the head-group kernel also covers D = 64 FP8 pools, which the per-head kernel does not
+  const bool hg_ok = decode_hg_enabled() && decode_fast_layout_ok(p, a->kv_dtype) &&
+                     decode_hg_supported(p, a->q_dtype, a->kv_dtype);
+  const bool fast_ok = hg_ok || (decode_fast_supported(a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype) &&
+                                 decode_fast_layout_ok(p, a->kv_dtype));
   B200_CHECK_ARG(!(a->kernel == B200_KERNEL_FAST && !fast_ok),
                  "decode: fast kernel does not cover Dk=%d Dv=%d group=%d q=%d kv=%d (or unaligned strides)",
                  a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype);
   const bool use_fast = fast_ok && a->kernel != B200_KERNEL_GENERIC;
   int rc;
   if (a->ev_attn_start) B200_CHECK_CUDA(cudaEventRecord(reinterpret_cast<cudaEvent_t>(a->ev_attn_start), stream));
-  const bool use_hg = use_fast && decode_hg_enabled() && decode_hg_supported(p, a->q_dtype, a->kv_dtype);
+  const bool use_hg = use_fast && hg_ok;
   if (use_hg) {
     rc = launch_decode_hg(p, a->q_dtype, a->kv_dtype, a->num_ctas, stream);
   } else if (use_fast) {

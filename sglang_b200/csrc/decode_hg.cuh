@@ -27,12 +27,22 @@ struct HgCfg {
   static constexpr int kStages = kStageB <= 16 * 1024 ? 4 : 3;
   static constexpr int kRingB = kStages * kStageB;
   static constexpr int kCtaSmem = kRingB + 16 * kStages;
-  static constexpr int kLdPerTok = kTokB / 512;          // full-warp cp.async per token per tensor
+  static constexpr int kLdPerTok = kTokB / 512;          // full-warp cp.async per token per tensor (0: half a warp)
   static constexpr int kTokPerWarp = kTileTok / kHG;     // tokens each warp gathers per stage
   static constexpr int kNT = D / 8;                      // output n-tiles
-  static constexpr int kMinBlocks = kCtaSmem > 110 * 1024 ? 1 : (kCtaSmem <= 72 * 1024 ? 3 : 2);
-  static_assert(kCpr >= 8 && kCpr % 8 == 0, "head rows must be whole 128-byte lines");
-  static_assert(kTokB % 512 == 0, "a token slice must be whole full-warp copies");
+#ifndef B200_HG_SMALL_BLOCKS
+#define B200_HG_SMALL_BLOCKS 4
+#endif
+  // 8 KiB stages (D = 64 FP8): half the bytes per tile behind the same per-tile dependency chain, so more resident
+  // warps are what hides it
+  static constexpr int kMinBlocks =
+      kCtaSmem > 110 * 1024 ? 1 : (kCtaSmem <= 36 * 1024 ? B200_HG_SMALL_BLOCKS : (kCtaSmem <= 72 * 1024 ? 3 : 2));
+  // D = 64 FP8 pools: a head row is 64 bytes (4 chunks), the 4-head slice 256 bytes = HALF a warp's cp.async, so one
+  // copy instruction covers two tokens and the swizzle runs over chunk indices that span two heads
+  static constexpr bool kHalfWarpTok = kTokB == 256;
+  static_assert(kCpr % 8 == 0 || (kCpr == 4 && kFp8), "head rows: whole 128-byte lines, or 64-byte FP8 rows");
+  static_assert(kTokB % 512 == 0 || kHalfWarpTok, "a token slice must be whole (or exactly half) full-warp copies");
+  static_assert(!kHalfWarpTok || kTokPerWarp % 2 == 0, "half-warp copies take tokens in pairs");
 };
 
 template <int D, int KV, typename QT, bool UPPER>
@@ -133,6 +143,18 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
       if (n_issue >= (uint32_t)C::kStages)
         ptx::mbar_wait(bar_empty + 8 * stage, ((n_issue / C::kStages) - 1) & 1, 100 + stage);
       const uint32_t kst = ring + stage * C::kStageB, vst = kst + C::kTileB;
+      if constexpr (C::kHalfWarpTok) {
+#pragma unroll
+        for (int k = 0; k < C::kTokPerWarp / 2; ++k) {                     // lanes 0-15: one token, 16-31: the next
+          const int tok = warp * C::kTokPerWarp + 2 * k + (lane >> 4);
+          const int ch = lane & 15;                                        // 16-byte chunk of the 4-head slice
+          const int64_t slot = __shfl_sync(0xffffffffu, pt_cur, (T & 1) * 16 + tok);
+          const bool valid = T * kTileTok + tok < n_tok;
+          const uint32_t off = tok * C::kTokB + ((ch ^ (tok & 7)) << 4);
+          cp_async_16(kst + off, kc + slot * k_slot_b + ch * 16, valid);
+          cp_async_16(vst + off, vc + slot * v_slot_b + ch * 16, valid);
+        }
+      } else {
 #pragma unroll
       for (int k = 0; k < C::kTokPerWarp; ++k) {
         const int tok = warp * C::kTokPerWarp + k;
@@ -146,6 +168,7 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
           cp_async_16(vst + off, vc + slot * v_slot_b + ch * 16, valid);
         }
       }
+      }
       ptx::cp_async_mbar_arrive_noinc(bar_full + 8 * stage);
       ++n_issue;
     };
@@ -158,7 +181,14 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
       if (T + C::kStages - 1 < n_tiles) issue(T + C::kStages - 1);
       const uint32_t stage = n_cons % C::kStages;
       ptx::mbar_wait(bar_full + 8 * stage, (n_cons / C::kStages) & 1, 110 + stage);
-      const uint32_t kst = ring + stage * C::kStageB + warp * C::kRowB, vst = kst + C::kTileB;
+      // this warp's head inside the stage: whole 128-byte lines sit beside each other, so the head offset is added
+      // outside the swizzle; 64-byte rows (D = 64 FP8) share a line with the neighbouring head and the head's first
+      // chunk goes through the XOR with the token's row instead (soff)
+      const uint32_t kst = ring + stage * C::kStageB + (C::kCpr % 8 == 0 ? warp * C::kRowB : 0), vst = kst + C::kTileB;
+      auto soff = [&](int tok, int ch, int r) -> uint32_t {     // r == tok & 7
+        if constexpr (C::kCpr % 8 == 0) return tok * C::kTokB + ((ch ^ r) << 4);
+        else return tok * C::kTokB + (((warp * C::kCpr + ch) ^ r) << 4);
+      };
 
       // ---- S = Q K^T (16 heads x 16 tokens) ----
       float s_acc[2][4];
@@ -170,7 +200,7 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
           const int r = lane & 7, mi = lane >> 3;
           const int tok = r + 8 * (mi >> 1), ch = 2 * ks + (mi & 1);
           uint32_t b[4];
-          ldmatrix_x4(b, kst + tok * C::kTokB + ((ch ^ r) << 4));
+          ldmatrix_x4(b, kst + soff(tok, ch, r));
           mma16816<CT>(s_acc[0], QA(ks, 0), QA(ks, 1), QA(ks, 2), QA(ks, 3), b[0], b[1]);
           mma16816<CT>(s_acc[1], QA(ks, 0), QA(ks, 1), QA(ks, 2), QA(ks, 3), b[2], b[3]);
         }
@@ -180,7 +210,7 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
           const int r = lane & 7, mi = lane >> 3;
           const int tok = r + 8 * (mi & 1), ch = c2 + (mi >> 1);
           uint32_t b[4];
-          ldmatrix_x4(b, kst + tok * C::kTokB + ((ch ^ r) << 4));
+          ldmatrix_x4(b, kst + soff(tok, ch, r));
 #pragma unroll
           for (int u = 0; u < 2; ++u) {
             const int ks = c2 + u;
@@ -256,7 +286,7 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
           const int r = lane & 7;
           const int tok = r + 8 * ((lane >> 3) & 1), ch = j + (lane >> 4);
           uint32_t b[4];
-          ldmatrix_x4_trans(b, vst + tok * C::kTokB + ((ch ^ r) << 4));
+          ldmatrix_x4_trans(b, vst + soff(tok, ch, r));
           mma16816<CT>(o[j], pa[0], pa[1], pa[2], pa[3], b[0], b[1]);
           mma16816<CT>(o[j + 1], pa[0], pa[1], pa[2], pa[3], b[2], b[3]);
         }
@@ -266,7 +296,7 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
           const int r = lane & 7;
           const int tok = r + 8 * ((lane >> 3) & 1), ch = j + (lane >> 4);
           uint32_t b[4];
-          ldmatrix_x4_trans(b, vst + tok * C::kTokB + ((ch ^ r) << 4));
+          ldmatrix_x4_trans(b, vst + soff(tok, ch, r));
 #pragma unroll
           for (int u = 0; u < 2; ++u) {
             // bytes [t0 d, t0 d+1, t1 d, t1 d+1] -> [t0 d, t1 d | t0 d+1, t1 d+1]
@@ -332,10 +362,19 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
   }
 }
 
+// head dims / dtypes the head-group kernel has an instance for: everything the per-head kernel covers plus D = 64
+// with FP8 pools (64-byte rows, below the 128-byte ldmatrix line the per-head kernel is laid out for; here the
+// 4-head slice of a token is 256 contiguous bytes, which is all the layout needs)
+bool decode_hg_dims_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype) {
+  if (decode_fast_supported(dqk, dv, group, q_dtype, kv_dtype)) return true;
+  const bool fp8 = kv_dtype == B200_FP8_E4M3 || kv_dtype == B200_FP8_E5M2;
+  return fp8 && dqk == 64 && dv == 64 && group >= 1 && group <= 16 && (q_dtype == B200_BF16 || q_dtype == B200_F16);
+}
+
 bool decode_hg_supported(const DecodeParams& p, int q_dtype, int kv_dtype) {
   const int D = p.head_dim_qk;
   if (p.num_kv_heads % kHG != 0) return false;
-  if (!decode_fast_supported(D, p.head_dim_v, p.group, q_dtype, kv_dtype)) return false;
+  if (!decode_hg_dims_supported(D, p.head_dim_v, p.group, q_dtype, kv_dtype)) return false;
   if (D == 256 && kv_dtype != B200_FP8_E4M3) return false;     // 192 KiB ring: keep the per-head kernel
   const int esz = (kv_dtype == B200_FP8_E4M3 || kv_dtype == B200_FP8_E5M2) ? 1 : 2;
   // the 4 heads of a group must be contiguous in a pool row; outputs must take 8-byte vector stores
@@ -368,9 +407,11 @@ int launch_decode_hg_q(const DecodeParams& p, int kv_dtype, int num_ctas, cudaSt
   constexpr int kSame = dtype_of<QT>::value;
   const int D = p.head_dim_qk;
   if (kv_dtype == B200_FP8_E4M3) {
+    if (D == 64) return launch_decode_hg_d<64, B200_FP8_E4M3, QT>(p, num_ctas, stream);
     if (D == 128) return launch_decode_hg_d<128, B200_FP8_E4M3, QT>(p, num_ctas, stream);
     if (D == 256) return launch_decode_hg_d<256, B200_FP8_E4M3, QT>(p, num_ctas, stream);
   } else if (kv_dtype == B200_FP8_E5M2) {
+    if (D == 64) return launch_decode_hg_d<64, B200_FP8_E5M2, QT>(p, num_ctas, stream);
     if (D == 128) return launch_decode_hg_d<128, B200_FP8_E5M2, QT>(p, num_ctas, stream);
   } else {
     if (D == 64) return launch_decode_hg_d<64, kSame, QT>(p, num_ctas, stream);
@@ -390,7 +431,7 @@ int decode_hg_ctas_per_sm(int head_dim, int kv_dtype) {
   const bool fp8 = kv_dtype == B200_FP8_E4M3 || kv_dtype == B200_FP8_E5M2;
   const int stage = 2 * kTileTok * kHG * head_dim * (fp8 ? 1 : 2);
   const int smem = (stage <= 16 * 1024 ? 4 : 3) * stage;
-  return smem > 110 * 1024 ? 1 : (smem <= 72 * 1024 ? 3 : 2);
+  return smem > 110 * 1024 ? 1 : (smem <= 36 * 1024 ? B200_HG_SMALL_BLOCKS : (smem <= 72 * 1024 ? 3 : 2));
 }
 
 }  // namespace

@@ -111,6 +111,44 @@ def test_decode_e5m2_fast_kernels(shape):
     assert float((got - gen).abs().max()) <= 2e-2
 
 
+D64_FP8_SHAPES = [
+    # bs, Hq, Hkv, D, lens, page
+    (3, 64, 8, 64, [1, 17, 1300], 1),          # gpt-oss heads (group 8), ragged incl. length 1
+    (2, 32, 8, 64, [515, 64], 16),             # Llama-3.2-1B heads (group 4), paged
+    (2, 64, 4, 64, [300, 129], 1),             # group 16 (upper MMA rows)
+    (4, 8, 8, 64, [33, 2, 700, 65], 1),        # MHA
+]
+
+
+@pytest.mark.parametrize("pool_dtype", [torch.float8_e4m3fn, torch.float8_e5m2], ids=["e4m3", "e5m2"])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "f16"])
+@pytest.mark.parametrize("shape", D64_FP8_SHAPES, ids=[f"bs{s[0]}_h{s[1]}_{s[2]}_p{s[5]}" for s in D64_FP8_SHAPES])
+def test_decode_d64_fp8_head_group_kernel(shape, dtype, pool_dtype):
+    """D = 64 FP8 pools (64-byte rows) on the tensor-core head-group kernel: half-warp token copies, swizzle across
+    two heads of a 128-byte line.  KERNEL_FAST refuses shapes it has no instance for, so passing proves the kernel ran."""
+    bs, Hq, Hkv, D, lens, page = shape
+    q, kp, vp, rtt, rpi, seq = _random_problem(bs, Hq, Hkv, D, lens, page, dtype, pool_dtype, seed=3 * bs + Hkv)
+    want = ref.decode_ref(q, kp, vp, rtt, rpi, seq, D**-0.5, kv_dtype=pool_dtype, k_scale=0.75, v_scale=1.5)
+    for kernel, chunk in ((2, 0), (0, 0), (2, 64)):       # FAST, AUTO, FAST with 64-token chunks (merge of many partials)
+        got, _ = _run_ops_decode(q, kp, vp, rtt, rpi, seq, D**-0.5, pool_dtype, kernel=kernel, fixed_chunk=chunk,
+                                 k_scale=0.75, v_scale=1.5)
+        assert_close_scaled(got, want, f"kernel {kernel} chunk {chunk}")
+    gen, _ = _run_ops_decode(q, kp, vp, rtt, rpi, seq, D**-0.5, pool_dtype, kernel=KERNELS["generic"], k_scale=0.75,
+                             v_scale=1.5)
+    assert float((got - gen).abs().max()) <= 2e-2
+
+
+def test_decode_d64_fp8_needs_four_kv_heads_for_the_fast_path():
+    """Hkv not a multiple of 4 (Qwen2.5-0.5B: 2 kv heads) keeps the CUDA-core kernel for D = 64 FP8 pools: AUTO works,
+    FAST refuses loudly."""
+    q, kp, vp, rtt, rpi, seq = _random_problem(2, 14, 2, 64, [515, 575], 1, torch.bfloat16, torch.float8_e4m3fn, seed=5)
+    want = ref.decode_ref(q, kp, vp, rtt, rpi, seq, 64**-0.5, kv_dtype=torch.float8_e4m3fn)
+    got, _ = _run_ops_decode(q, kp, vp, rtt, rpi, seq, 64**-0.5, torch.float8_e4m3fn, kernel=0)
+    assert_close_scaled(got, want)
+    with pytest.raises(Exception, match="fast kernel does not cover"):
+        _run_ops_decode(q, kp, vp, rtt, rpi, seq, 64**-0.5, torch.float8_e4m3fn, kernel=2)
+
+
 def test_decode_fp8_descale_and_logit_cap():
     q, kp, vp, rtt, rpi, seq = _random_problem(3, 8, 2, 128, [400, 3, 129], 1, torch.bfloat16,
                                                torch.float8_e4m3fn, seed=11)
