@@ -97,8 +97,9 @@ def decode_case(name, bs, L, Hq, Hkv, D, pool_dtype, page, iters, ragged=False, 
 
 
 def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_dtype=torch.bfloat16, tree_mask=False,
-                page=1, one_tile=False):
-    """`page` > 1: the pool is page-granular (random page order, slots consecutive inside a page -- what SGLang's
+                page=1, one_tile=False, splits=1):
+    """`splits`: 0 = what the backend picks for bs x Hkv one-tile items (ops.extend_pick_splits), > 1 = that many.
+    `page` > 1: the pool is page-granular (random page order, slots consecutive inside a page -- what SGLang's
     paged allocator hands out); P and E must be multiples of it."""
     dev = "cuda"
     g = torch.Generator(device=dev).manual_seed(0)
@@ -139,15 +140,22 @@ def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_d
         mkw = dict(custom_mask=m.reshape(-1), mask_skip_prefix=True,
                    mask_indptr=torch.arange(bs + 1, device=dev, dtype=torch.int64) * (E * (P + E)))
 
+    if splits == 0:
+        splits = ops.extend_pick_splits(bs * Hkv, sm)
+    if splits > 1:
+        mkw.update(num_splits=splits, split_ws=torch.empty(ops.extend_split_ws_floats(splits, T, Hq, D), device=dev))
+
     def fn():
         ops.extend_attention(q, o, kp, vp, rtt, rpi, pre, ext, ws, D**-0.5, kernel=kernel, kv_dtype=pool_dtype,
                              page_size=page, **mkw)
 
     t = time_cuda(fn, iters, warmup=2)
+    if t < 500e-6:      # short-extend launches run under CUDA graphs in the engine (speculative decoding)
+        t = min(t, time_cuda_graph(fn))
     flops = 4 * Hq * D * bs * (E * P + E * (E + 1) / 2)
     tf = flops / t / 1e12
     return dict(case=name, kind="extend", ms=round(t * 1e3, 3), tflops=round(tf, 1), frac_measured=round(tf / TF, 3),
-                frac_nominal=round(tf / 2250, 3), page_size=page, page_box_rows=int(ws.plan[4]))
+                frac_nominal=round(tf / 2250, 3), page_size=page, page_box_rows=int(ws.plan[4]), splits=splits)
 
 
 def store_case(name, T, Hkv, D, pool_dtype, iters):
@@ -226,6 +234,17 @@ def main():
         emit(decode_case("D64 gpt-oss heads 64/8 fp8 bs64 ctx8192, generic kernel", 64, 8192, 64, 8, 64, e4, 1,
                          max(3, a.iters // 10), kernel=1))
         emit(decode_case("D64 llama-3.2-1b heads 32/8 fp8 bs128 ctx8192 page16", 128, 8192, 32, 8, 64, e4, 16, a.iters))
+    if a.only in ("", "extend", "verify"):
+        # speculative verify (tree mask over 8 draft tokens) and short extends at several batch sizes: unsplit
+        # one-tile items against the split-KV the backend picks from bs x Hkv
+        it = max(5, a.iters // 3)
+        for bs, P in ((64, 4096), (16, 4096), (4, 4096), (1, 4096), (1, 32768), (8, 16384), (64, 512)):
+            for sp in (1, 0):
+                emit(extend_case(f"verify {bs} req x ({P} + 8 draft, tree mask), one-tile, splits {'auto' if sp == 0 else sp}",
+                                 bs, P, 8, 32, 8, 128, it, shared=False, tree_mask=True, one_tile=True, splits=sp))
+        for sp in (1, 0):
+            emit(extend_case(f"short extend 8 req x (8192 + 16 new), one-tile, splits {'auto' if sp == 0 else sp}", 8, 8192,
+                             16, 32, 8, 128, it, shared=False, one_tile=True, splits=sp))
     if a.only in ("", "store"):
         emit(store_case("decode store 64 rows 8B bf16", 64, 8, 128, bf, a.iters))
         emit(store_case("decode store 256 rows 8B fp8", 256, 8, 128, e4, a.iters))

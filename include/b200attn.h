@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 5
+#define B200ATTN_ABI_VERSION 6
 
 typedef void* b200_stream_t; /* a cudaStream_t */
 
@@ -290,9 +290,25 @@ typedef struct b200_extend_args {
   int32_t page_size;            /* KV page size of the pool (req_to_token entries of one page are consecutive slots,
                                    pages are page_size-aligned); >= 16 lets the fill use one TMA box per page; 0/1 =
                                    token-granular */
+  /* Split-KV for one-tile plans (block_q == 128 / group: TARGET_VERIFY / DRAFT_EXTEND / a few new tokens behind a long
+   * prefix), where bs x Hkv work items cannot fill 148 SMs: every item's kv range is cut into up to num_splits
+   * parts (the device trims that per item so that a part keeps >= 4 kv blocks), each part is its own CTA writing a
+   * normalised fp32 partial + base-2 LSE to split_ws, and a merge launch combines them (sinks, v_scale and the LSE
+   * output applied there).  The reference's Triton extend kernel has no such split (extend_attention.py:664-812 walks
+   * the whole prefix per program); its decode kernel does (decode_attention.py:968-1044).  0 / 1 = off. */
+  int32_t num_splits;
+  float* split_ws;              /* >= b200attn_extend_split_ws_floats(...) floats; required when num_splits > 1 */
+  int64_t split_ws_floats;      /* capacity of split_ws */
 } b200_extend_args;
 
 int b200attn_extend(const b200_extend_args* args, b200_stream_t stream);
+/* floats of split workspace b200attn_extend needs for num_splits > 1 */
+int64_t b200attn_extend_split_ws_floats(int32_t num_splits, int64_t num_q_tokens, int32_t num_q_heads, int32_t head_dim_v);
+/* split count that fills `num_sms` SMs best for `items` one-tile work items (bs x Hkv for speculative batches) of about
+ * `kv_tokens_hint` kv tokens each (0 = unknown, e.g. under CUDA-graph capture: 4096 is assumed); 1 when the items already
+ * make several waves or a split would not pay for its fixed costs */
+int32_t b200attn_extend_pick_splits(int32_t items, int32_t num_sms, int32_t kv_tokens_hint);
+#define B200_EXTEND_MAX_SPLITS 16
 int b200attn_extend_fast_supported(int32_t head_dim_qk, int32_t head_dim_v, int32_t group,
                                    int32_t q_dtype, int32_t kv_dtype);
 /* query tokens per tile the kernel that would be picked uses (for the plan) */

@@ -53,6 +53,10 @@ class _ExtendState:
 
     def __init__(self, ws, max_bs, mask, device):
         self.ws, self.max_bs, self.max_tiles, self.mask = ws, max_bs, ws.max_tiles, mask
+        self.device = device
+        # split-KV partials of one-tile plans: grown on demand; a buffer a captured graph may hold is never freed
+        self.split_ws = None
+        self._split_keep = []
         self._ext = {dt: torch.zeros(max_bs, dtype=dt, device=device) for dt in (torch.int32, torch.int64)}
         self._pre = {dt: torch.zeros(max_bs, dtype=dt, device=device) for dt in (torch.int32, torch.int64)}
         self.mask_indptr = torch.zeros(max_bs + 1, dtype=torch.int64, device=device)
@@ -65,6 +69,12 @@ class _ExtendState:
 
     def fits(self, bs, tiles, mask_bytes) -> bool:
         return bs <= self.max_bs and tiles <= self.max_tiles and mask_bytes <= self.mask.numel()
+
+    def split_buffer(self, floats: int) -> torch.Tensor:
+        if self.split_ws is None or self.split_ws.numel() < floats:
+            self.split_ws = torch.empty(int(floats), dtype=torch.float32, device=self.device)
+            self._split_keep.append(self.split_ws)
+        return self.split_ws
 
     def ext_lens(self, dtype):
         return self._ext[dtype]
@@ -146,6 +156,8 @@ class B200AttnBackend(_Base):
         self._one_tile_block_q = ops.extend_block_q_one_tile(self.head_dim, self.v_head_dim, group, self._q_dtype,
                                                              self.kv_dtype, self.extend_kernel)
         self._ext_block_q = self._extend_block_q      # block_q of the current forward's plan
+        self._ext_splits, self._ext_split_ws = 1, None      # split-KV choice of the current forward (one-tile plans)
+        self._ext_short = False                               # the host knows that no request extends by more than one tile
         self.num_draft_tokens = _spec_num_draft_tokens(model_runner)
         self.forward_metadata = None
         #: optional (start, stop) torch.cuda.Event pair re-recorded around the next decode attention kernel
@@ -260,6 +272,7 @@ class B200AttnBackend(_Base):
                 torch.cumsum((pre.to(torch.int64) + n) * n, dim=0, out=mask_indptr[1:])
                 mask = st.mask
             self._ext, self._ext_lens = st, (pre, ext, mask, mask_indptr)
+            self._plan_splits(bs, bs * n, self._kv_hint(forward_batch, bs, in_capture))
         elif not eager_lens and mode.is_draft_extend_v2():
             # CUDA-graph draft-extend: a fixed number of query rows per request; the cached prefix is
             # seq_lens - accepted tokens, clamped for padded rows (triton_backend.py:529-565)
@@ -278,6 +291,7 @@ class B200AttnBackend(_Base):
             else:
                 pre.copy_(seq)
             self._ext, self._ext_lens = st, (pre, ext, None, None)
+            self._plan_splits(bs, bs * n, self._kv_hint(forward_batch, bs, in_capture))
         else:
             T = getattr(forward_batch, "extend_num_tokens", None)
             if T is None:
@@ -286,6 +300,30 @@ class B200AttnBackend(_Base):
             self._ext_block_q = self._pick_block_q(max(lens_cpu) if lens_cpu is not None and len(lens_cpu) else None)
             self._ext = self._select_ext((int(mode), bs), bs, int(T), 0, in_capture)
             self._ext_lens = (forward_batch.extend_prefix_lens, forward_batch.extend_seq_lens, None, None)
+            self._plan_splits(bs, int(T), self._kv_hint(forward_batch, bs, in_capture))
+
+    @staticmethod
+    def _kv_hint(forward_batch, bs: int, in_capture: bool) -> int:
+        """Mean context length per request from the host-side `seq_lens_sum` (0 = unknown: capture batches hold fill
+        values)."""
+        total = getattr(forward_batch, "seq_lens_sum", None)
+        if in_capture or bs <= 0 or not isinstance(total, int) or total <= 0:
+            return 0
+        return total // bs
+
+    def _plan_splits(self, bs: int, tokens: int, kv_hint: int = 0):
+        """Split-KV for one-tile plans (speculative verify / draft extend / a few new tokens): bs x Hkv work items
+        rarely fill the SMs, so every item's kv range is cut into parts (ops.extend_pick_splits; the device trims the
+        count for short contexts).  Under capture it is chosen from the batch shape alone (a graph keeps its choice);
+        eager batches add the mean context length (`seq_lens_sum`, a host int) as a hint."""
+        self._ext_splits, self._ext_split_ws = 1, None
+        if not self._ext_short or bs <= 0 or tokens <= 0:       # (D = 256 plans are always one-tile: long prefills stay unsplit)
+            return
+        s = ops.extend_pick_splits(bs * self.num_kv_head, self.sm_count, kv_hint)
+        if s > 1:
+            self._ext_splits = s
+            self._ext_split_ws = self._ext.split_buffer(
+                ops.extend_split_ws_floats(s, tokens, self.num_head, self.v_head_dim))
 
     def init_forward_metadata_in_graph(self, forward_batch):
         """One planner launch (static shape, graph-recordable, no host sync, reads persistent buffers only)."""
@@ -313,9 +351,9 @@ class B200AttnBackend(_Base):
     def _pick_block_q(self, max_extend_len) -> int:
         """Query tokens per work item for this forward: one-tile items when the host knows that no request extends
         by more than one tile's worth of tokens (every request then is exactly one item), else two-tile items."""
-        if self._one_tile_block_q and max_extend_len is not None and 0 < int(max_extend_len) <= self._one_tile_block_q:
-            return self._one_tile_block_q
-        return self._extend_block_q
+        self._ext_short = bool(self._one_tile_block_q and max_extend_len is not None
+                               and 0 < int(max_extend_len) <= self._one_tile_block_q)
+        return self._one_tile_block_q if self._ext_short else self._extend_block_q
 
     # ------------------------------------------------------------------ CUDA graphs
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
@@ -463,6 +501,7 @@ class B200AttnBackend(_Base):
             kernel=self.extend_kernel, lse=lse,
             window_keys=self._window_keys(layer) if causal else 0, sinks=self._sinks(kwargs, q.device),
             custom_mask=custom_mask, mask_indptr=mask_indptr, mask_skip_prefix=True, page_size=self.page_size,
+            num_splits=self._ext_splits, split_ws=self._ext_split_ws,
         )
         if lse is not None:
             return o.view(T, layer.tp_q_head_num, layer.v_head_dim), lse

@@ -157,7 +157,16 @@ struct ExtendParams {
   const float* sinks;           // [Hq] natural-log sink logits or nullptr
   const uint8_t* custom_mask;   // see b200_extend_args
   const int64_t* mask_indptr;
+  // split-KV of one-tile items (num_splits > 1): partial s of q row i, head h lives at
+  //   split_o  [((s * num_q_tokens + i) * Hq + h) * Dv ...]   normalised fp32
+  //   split_lse[ (s * num_q_tokens + i) * Hq + h ]            base-2 LSE of the part; -inf: the part saw nothing;
+  //                                                           +inf (split 0 only): o / lse already hold the final row
+  int32_t num_splits;
+  float* split_o;
+  float* split_lse;
 };
+
+constexpr int kSplitMinBlocks = 4;   // a split part keeps at least this many kv blocks (the device trims num_splits per item)
 
 // ----------------------------------------------------------------------------
 // generic kernel: one warp per (q token, q head); any head_dim <= 512 / dtype pair.
@@ -269,6 +278,88 @@ extern "C" int b200attn_extend_plan(const b200_extend_plan_args* a, b200_stream_
   return B200_OK;
 }
 
+namespace b200 {
+namespace {
+// Merge of the split-KV partials of one-tile items: one warp per (q row, q head); lane s holds split s's LSE.
+//   out = v_scale * sum_s 2^(lse_s - m) o_s / (sum_s 2^(lse_s - m) + 2^(sink - m))
+constexpr int kSplitMergeWarps = 4;
+
+template <typename QT>
+__global__ void __launch_bounds__(kSplitMergeWarps* kWarp) extend_split_merge_kernel(const ExtendParams p) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int Hq = p.num_q_heads, D = p.head_dim_v, S = p.num_splits;
+  const int64_t rows = (int64_t)p.plan[3] * Hq;                       // sum E_r (device-side) x heads
+  const int64_t idx = (int64_t)blockIdx.x * kSplitMergeWarps + warp;
+  if (idx >= rows || idx >= p.num_q_tokens * Hq) return;
+  const int64_t tok = idx / Hq;
+  const int h = (int)(idx - tok * Hq);
+  const int64_t part = p.num_q_tokens * Hq;                           // rows per split
+  const float l = lane < S ? p.split_lse[lane * part + idx] : -INFINITY;
+  if (__shfl_sync(0xffffffffu, l, 0) == INFINITY) return;             // the item was not split: split 0 wrote the row
+  const float m = warp_max(l);
+  QT* orow = reinterpret_cast<QT*>(p.o) + tok * p.o_stride_t + (int64_t)h * p.o_stride_h;
+  if (m == -INFINITY) {                                               // no part saw a key (cannot happen under the
+    for (int d = lane; d < D; d += kWarp) orow[d] = from_float<QT>(0.f);   // causal rule; kept for masks)
+    if (p.lse != nullptr && lane == 0) p.lse[idx] = -INFINITY;
+    return;
+  }
+  const float w = lane < S ? fast_exp2(l - m) : 0.f;                  // 2^(-inf) = 0 for empty parts
+  float den = w;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) den += __shfl_xor_sync(0xffffffffu, den, o);
+  if (p.sinks != nullptr) den += exp2f(p.sinks[h] * kLog2e - m);
+  const float inv = p.v_scale / den;
+  for (int d = lane * 4; d < D; d += 4 * kWarp) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int s = 0; s < S; ++s) {
+      const float ws = __shfl_sync(0xffffffffu, w, s);
+      if (ws > 0.f) {                                                 // parts with lse = -inf hold no data
+        const float4 v = *reinterpret_cast<const float4*>(p.split_o + (s * part + idx) * D + d);
+        acc.x = fmaf(ws, v.x, acc.x); acc.y = fmaf(ws, v.y, acc.y);
+        acc.z = fmaf(ws, v.z, acc.z); acc.w = fmaf(ws, v.w, acc.w);
+      }
+    }
+    *reinterpret_cast<uint2*>(orow + d) = make_uint2(pack2<QT>(acc.x * inv, acc.y * inv), pack2<QT>(acc.z * inv, acc.w * inv));
+  }
+  if (p.lse != nullptr && lane == 0) p.lse[idx] = (m + log2f(den)) * kLn2;
+}
+
+int launch_split_merge(const ExtendParams& p, int q_dtype, cudaStream_t stream) {
+  const int64_t rows = p.num_q_tokens * p.num_q_heads;
+  const unsigned grid = (unsigned)((rows + kSplitMergeWarps - 1) / kSplitMergeWarps);
+  if (q_dtype == B200_BF16) extend_split_merge_kernel<__nv_bfloat16><<<grid, kSplitMergeWarps * kWarp, 0, stream>>>(p);
+  else extend_split_merge_kernel<__half><<<grid, kSplitMergeWarps * kWarp, 0, stream>>>(p);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+}  // namespace
+}  // namespace b200
+
+extern "C" int64_t b200attn_extend_split_ws_floats(int32_t num_splits, int64_t num_q_tokens, int32_t num_q_heads,
+                                                   int32_t head_dim_v) {
+  if (num_splits <= 1) return 0;
+  return (int64_t)num_splits * num_q_tokens * num_q_heads * ((int64_t)head_dim_v + 1);
+}
+
+extern "C" int32_t b200attn_extend_pick_splits(int32_t items, int32_t num_sms, int32_t kv_tokens_hint) {
+  if (items <= 0 || num_sms <= 0 || items > 8 * num_sms) return 1;    // >= 8 waves: the quantisation loss is small
+  // Makespan in units of one unsplit item: ceil(items * S / SMs) waves, each 1 / S of an item plus the fixed cost of a
+  // part (TMEM allocation, Q fill, pipeline ramp, fp32 partial epilogue: ~6.5 us = 4 kv blocks of 1.64 us, measured
+  // on the 64 x (4 K + 8) verify shape), plus the merge launch (~6 us) once.  A split has to win by 5 %.
+  const double blocks = (kv_tokens_hint > 0 ? kv_tokens_hint : 4096) / 128.0 + 1.0;
+  const double part_cost = 4.0 / blocks, merge_cost = 3.7 / blocks;
+  const int w1 = (items + num_sms - 1) / num_sms;
+  const double unsplit = w1 * (1.0 + part_cost);
+  int best = 1;
+  double best_cost = unsplit * 0.95;
+  for (int S = 2; S <= B200_EXTEND_MAX_SPLITS; ++S) {
+    const int waves = (items * S + num_sms - 1) / num_sms;
+    const double cost = waves * (1.0 / S + part_cost) + merge_cost;
+    if (cost < best_cost - 1e-9) { best_cost = cost; best = S; }
+  }
+  return best;
+}
+
 extern "C" int b200attn_extend_fast_supported(int32_t dqk, int32_t dv, int32_t group, int32_t q_dtype,
                                               int32_t kv_dtype) {
   return b200::extend_fast_supported(dqk, dv, group, q_dtype, kv_dtype) ? 1 : 0;
@@ -315,6 +406,7 @@ extern "C" int b200attn_extend(const b200_extend_args* a, b200_stream_t stream_)
   p.window_keys = a->window_keys > 0 ? a->window_keys : 0; p.sinks = a->sinks;
   p.custom_mask = a->custom_mask; p.mask_indptr = a->mask_indptr; p.mask_skip_prefix = a->mask_skip_prefix;
   p.kv_e5m2 = a->kv_dtype == B200_FP8_E5M2;
+  p.num_splits = 1; p.split_o = nullptr; p.split_lse = nullptr;
   p.tma_rows = 0;
   p.pool_slots = a->pool_slots > 0 && a->pool_slots < 0x7fffffff ? (int32_t)a->pool_slots : 0;
   B200_CHECK_ARG(a->custom_mask == nullptr || a->mask_indptr != nullptr, "extend: custom_mask needs mask_indptr");
@@ -326,6 +418,26 @@ extern "C" int b200attn_extend(const b200_extend_args* a, b200_stream_t stream_)
                  "extend: fast kernel does not cover Dk=%d Dv=%d group=%d q=%d kv=%d (or unaligned strides)",
                  a->head_dim_qk, a->head_dim_v, p.group, a->q_dtype, a->kv_dtype);
   const bool use_fast = fast_ok && a->kernel != B200_KERNEL_GENERIC;
+  if (a->num_splits > 1) {
+    B200_CHECK_ARG(a->num_splits <= B200_EXTEND_MAX_SPLITS, "extend: num_splits %d > %d", a->num_splits,
+                   B200_EXTEND_MAX_SPLITS);
+    B200_CHECK_ARG(use_fast && a->block_q == extend_fast_block_q_one_tile(p.group),
+                   "extend: num_splits %d needs the tcgen05 kernel's one-tile plan (block_q %d, got %d)", a->num_splits,
+                   extend_fast_block_q_one_tile(p.group), a->block_q);
+    const int64_t need = b200attn_extend_split_ws_floats(a->num_splits, a->num_q_tokens, a->num_q_heads, a->head_dim_v);
+    B200_CHECK_ARG(a->split_ws != nullptr && a->split_ws_floats >= need && ((uintptr_t)a->split_ws & 15) == 0,
+                   "extend: split workspace of %lld floats (16-byte aligned) needed for %d splits, got %lld",
+                   (long long)need, a->num_splits, (long long)a->split_ws_floats);
+    B200_CHECK_ARG(a->o_stride_t % 4 == 0 && a->o_stride_h % 4 == 0 && ((uintptr_t)a->o & 7) == 0,
+                   "extend: split merge writes 8-byte vectors: o strides must be multiples of 4 elements");
+    p.num_splits = a->num_splits;
+    p.split_o = a->split_ws;
+    // the LSE block starts 16-byte aligned as well: S * T * Hq * Dv floats with Dv a multiple of 64
+    p.split_lse = a->split_ws + (int64_t)a->num_splits * a->num_q_tokens * a->num_q_heads * a->head_dim_v;
+    const int rc = launch_extend_fast(p, *a, stream);
+    if (rc != B200_OK) return rc;
+    return launch_split_merge(p, a->q_dtype, stream);
+  }
   if (use_fast) return launch_extend_fast(p, *a, stream);
   if (a->q_dtype == B200_BF16) return launch_generic<__nv_bfloat16>(p, a->kv_dtype, a->num_ctas, stream);
   return launch_generic<__half>(p, a->kv_dtype, a->num_ctas, stream);

@@ -193,7 +193,11 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
 
   // ---- work item -----------------------------------------------------------------------------
   const int Hkv = p.num_kv_heads, g = p.group;
-  const int item_tile = blockIdx.x / Hkv, kvh = blockIdx.x - item_tile * Hkv;
+  // split-KV (one-tile instances only): blockIdx.x = (item_tile * num_splits + split) * Hkv + kvh
+  const int n_splits = kOneTile ? p.num_splits : 1;
+  const int item_part = blockIdx.x / Hkv, kvh = blockIdx.x - item_part * Hkv;
+  const int item_tile = kOneTile ? item_part / n_splits : item_part;
+  const int split = kOneTile ? item_part - item_tile * n_splits : 0;
   const int num_tiles = p.plan[0];
   if (item_tile >= num_tiles || item_tile >= max_tiles) return;
   const int32_t* qo_indptr = p.plan + kPlanHeader;
@@ -212,8 +216,33 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
   // 128-token blocks below that are skipped; all three roles count blocks from kv_off
   const int kv_first =
       (kOpts && p.window_keys > 0 && P + q_start + 1 > p.window_keys) ? P + q_start + 1 - p.window_keys : 0;
-  const int kv_off = kv_first / kBlockKV * kBlockKV;
-  const int n_blocks = (kv_end - kv_off + kBlockKV - 1) / kBlockKV;
+  const int kv_off_item = kv_first / kBlockKV * kBlockKV;
+  const int n_blocks_item = (kv_end - kv_off_item + kBlockKV - 1) / kBlockKV;
+  // This CTA's part of the item's kv blocks.  The split count is trimmed per item so that a part keeps at least
+  // kSplitMinBlocks blocks; parts beyond it only report "saw nothing" (LSE -inf), and an item left with ONE part is
+  // finished by split 0 exactly like an unsplit item (it flags its rows with LSE +inf so that the merge skips them).
+  int kv_off_part = kv_off_item, n_blocks_part = n_blocks_item;
+  bool partial = false;                                   // this CTA writes a partial to the split workspace
+  if constexpr (kOneTile) {
+    if (n_splits > 1) {
+      const int s_eff = max(1, min(n_splits, n_blocks_item / kSplitMinBlocks));
+      partial = s_eff > 1;
+      const int b0 = (int)((int64_t)n_blocks_item * split / s_eff), b1 = (int)((int64_t)n_blocks_item * (split + 1) / s_eff);
+      if (split >= s_eff || !partial) {
+        // rows of this item in the LSE block of this split: -inf (no data), or +inf from split 0 of an unsplit item
+        const int r = threadIdx.x;
+        const int tok = r / g;
+        if (r < 128 && r < BQ * g && tok < n_q)
+          p.split_lse[((int64_t)split * p.num_q_tokens + q_tok0 + tok) * p.num_q_heads + kvh * g + (r - tok * g)] =
+              (split == 0) ? INFINITY : -INFINITY;
+        if (split > 0) return;
+      } else {
+        kv_off_part = kv_off_item + b0 * kBlockKV;
+        n_blocks_part = b1 - b0;
+      }
+    }
+  }
+  const int kv_off = kv_off_part, n_blocks = n_blocks_part;
   // TMA page boxes only when the plan has verified that every box-sized run of positions of every request sits on
   // consecutive pool rows (b200attn_extend_plan); any other page table is read row by row
   const bool use_tma = kTma && p.plan[kPlanPageRows] == p.tma_rows;
@@ -365,8 +394,9 @@ int launch_extend_fast_t(const ExtendParams& p_in, const b200_extend_args& a, cu
   // host-side bound on the number of work items: sum_r ceil(E_r / block_q) <= T / block_q + bs
   int64_t tiles = a.num_q_tokens / block_q + a.batch_size;
   if (tiles > a.max_tiles) tiles = a.max_tiles;
-  const int64_t grid = tiles * p.num_kv_heads;
+  const int64_t grid = tiles * p.num_kv_heads * (kOneTile ? p.num_splits : 1);
   B200_CHECK_ARG(grid > 0 && grid < 0x7fffffff, "extend: bad grid %lld", (long long)grid);
+  B200_CHECK_ARG(kOneTile || p.num_splits == 1, "extend: split-KV needs the one-tile instance");
   kern<<<(unsigned)grid, tc::kThreads, kSmem, stream>>>(p, (int)tiles, tm_k, tm_v);
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;

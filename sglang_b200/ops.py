@@ -440,8 +440,13 @@ def extend_attention(
     mask_indptr: Optional[torch.Tensor] = None,
     mask_skip_prefix: bool = True,
     page_size: int = 1,
+    num_splits: int = 1,
+    split_ws: Optional[torch.Tensor] = None,
 ) -> torch.Tensor:
-    """`page_size`: KV page size of the pool (pages are page_size-aligned runs of consecutive slots).
+    """`num_splits` > 1 (one-tile plans only, see `extend_pick_splits`): split-KV -- every work item's kv range is cut
+    into up to `num_splits` parts that run as separate CTAs, `split_ws` (float32, >= `extend_split_ws_floats(...)`)
+    holds their partials and a merge launch follows.
+    `page_size`: KV page size of the pool (pages are page_size-aligned runs of consecutive slots).
     `window_keys` > 0: query at position x attends kv positions (x - window_keys, x].  `sinks`: float32 [Hq].
     `custom_mask` (uint8 / bool, flat) + `mask_indptr` (int64 [bs + 1]): request r, query i, kv position x is
     visible iff custom_mask[mask_indptr[r] + i * (P_r + E_r) + x]; it replaces the causal rule on the new tokens
@@ -489,9 +494,27 @@ def extend_attention(
         if mask_indptr.dtype != torch.int64 or mask_indptr.shape != (extend_seq_lens.shape[0] + 1,):
             raise ValueError("mask_indptr must be int64 [bs + 1]")
         a.custom_mask, a.mask_indptr = custom_mask.data_ptr(), mask_indptr.data_ptr()
+    if num_splits > 1:
+        if split_ws is None:
+            raise ValueError("num_splits > 1 needs split_ws")
+        _need_cuda(split_ws)
+        if split_ws.dtype != torch.float32 or not split_ws.is_contiguous():
+            raise ValueError("split_ws must be a contiguous float32 tensor")
+        a.num_splits, a.split_ws, a.split_ws_floats = int(num_splits), split_ws.data_ptr(), split_ws.numel()
     _C.check(_C.lib.b200attn_extend(C.byref(a), _stream()), "extend")
-    launch_count += 1
+    launch_count += 2 if num_splits > 1 else 1
     return o
+
+
+def extend_pick_splits(items: int, num_sms: int, kv_tokens_hint: int = 0) -> int:
+    """Split count for `items` one-tile work items (requests x kv heads) of about `kv_tokens_hint` kv tokens each
+    (0 = unknown) on `num_sms` SMs; 1 = no split."""
+    return int(_C.lib.b200attn_extend_pick_splits(int(items), int(num_sms), max(0, int(kv_tokens_hint))))
+
+
+def extend_split_ws_floats(num_splits: int, num_q_tokens: int, num_q_heads: int, head_dim_v: int) -> int:
+    return int(_C.lib.b200attn_extend_split_ws_floats(int(num_splits), int(num_q_tokens), int(num_q_heads),
+                                                      int(head_dim_v)))
 
 
 # --------------------------------------------------------------------------- merge of partial states
