@@ -381,6 +381,24 @@ class B200AttnBackend(_Base):
     def get_cuda_graph_seq_len_fill_value(self):
         return 1
 
+    def update_verify_buffers_to_fill_after_draft(self, spec_info, cuda_graph_bs):
+        """EAGLE with the overlapped plan stream prepares the verify metadata BEFORE the draft has produced the tree
+        (eagle_worker_common.py:505-535): the mask that init_forward_metadata_out_graph copied was not the final one.
+        The worker calls this hook after the draft; everything else this backend derives for TARGET_VERIFY depends
+        on `seq_lens` and the draft-token count only, so the tree mask is the one buffer to refresh (the Triton
+        backend lets the tree kernel write into its own `verify_mask` buffer and has nothing to redo,
+        triton_backend.py:1208-1215; this backend keeps `verify_mask` = None, so the worker hands the mask over in
+        `spec_info.custom_mask`)."""
+        mask = getattr(spec_info, "custom_mask", None)
+        lens = self._ext_lens
+        if mask is None or lens is None or lens[2] is None:
+            return
+        m = mask.view(torch.uint8) if mask.dtype == torch.bool else mask
+        if m.numel() > lens[2].numel():
+            raise ValueError(f"b200 backend: tree mask of {m.numel()} bytes exceeds the verify mask buffer "
+                             f"({lens[2].numel()} bytes) chosen by init_forward_metadata_out_graph")
+        lens[2][: m.numel()].copy_(m, non_blocking=True)
+
     # ------------------------------------------------------------------ KV write
     def _save_kv(self, layer, cache_loc, k, v):
         """Scatter the new rows straight into the pool's layer buffers (same layout and

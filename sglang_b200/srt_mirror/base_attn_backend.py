@@ -7,6 +7,21 @@ from abc import ABC
 
 class AttentionBackend(ABC):
     needs_cpu_seq_lens: bool = True
+    # class-level switches the runners read (base_attn_backend.py:45-48,102-115)
+    supports_ragged_verify_graph: bool = False
+    use_captured_forward_metadata_for_breakable_cuda_graph: bool = False
+    supports_full_cuda_graph_chunked_prefix: bool = False
+
+    def draft_extend_metadata_captured_in_graph(self) -> bool:
+        return False
+
+    @property
+    def verify_mask(self):
+        """The mask the draft stage fills in place, if the backend owns one (:172-175)."""
+        return None
+
+    def update_verify_buffers_to_fill_after_draft(self, spec_info, cuda_graph_bs):
+        raise NotImplementedError()
 
     def init_forward_metadata(self, forward_batch):
         """Eager entry point: `_out_graph` then `_in_graph` (base_attn_backend.py:50-56)."""

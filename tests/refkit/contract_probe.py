@@ -46,7 +46,8 @@ from sglang_b200.backend import B200AttnBackend  # noqa: E402
 # ---- ABC: the hooks the mirror declares exist in the reference with the same parameter names
 for name in ("init_forward_metadata", "init_forward_metadata_out_graph", "init_forward_metadata_in_graph",
              "init_cuda_graph_state", "get_cuda_graph_seq_len_fill_value", "on_after_cuda_graph_warmup",
-             "forward", "forward_decode", "forward_extend", "support_triton"):
+             "forward", "forward_decode", "forward_extend", "support_triton",
+             "update_verify_buffers_to_fill_after_draft", "draft_extend_metadata_captured_in_graph"):
     real = getattr(RealABC, name, None)
     check(real is not None, f"ABC.{name} exists in the reference")
     if real is None:
@@ -57,6 +58,14 @@ for name in ("init_forward_metadata", "init_forward_metadata_out_graph", "init_f
     check(rp == mp, f"ABC.{name} parameters: reference {rp} == mirror {mp}")
     check(bp[: len(rp)] == rp, f"B200AttnBackend.{name} accepts the reference's parameters {rp} (has {bp})")
 check(issubclass(B200AttnBackend, RealABC), "B200AttnBackend subclasses the reference ABC inside an SGLang process")
+# hooks whose ABC default raises must be overridden when a stock runner / speculative worker calls them on every
+# backend (decode_cuda_graph_runner.py:318, eagle_worker_common.py:527)
+for name in ("init_cuda_graph_state", "get_cuda_graph_seq_len_fill_value", "forward_decode", "forward_extend",
+             "update_verify_buffers_to_fill_after_draft"):
+    check(getattr(B200AttnBackend, name) is not getattr(RealABC, name), f"B200AttnBackend overrides ABC.{name}")
+for name in ("supports_ragged_verify_graph", "use_captured_forward_metadata_for_breakable_cuda_graph",
+             "supports_full_cuda_graph_chunked_prefix", "needs_cpu_seq_lens", "verify_mask"):
+    check(hasattr(RealABC, name) and hasattr(M.AttentionBackend, name), f"ABC.{name} exists in the reference and the mirror")
 
 # ---- ForwardMode: same member names and the predicates agree on every member
 for m in M.ForwardMode:

@@ -233,3 +233,15 @@ def test_backend_verify_picks_split_kv_and_matches_oracle():
     want2 = ref.extend_ref(pb.q, pb.kp, pb.vp, pb.rtt, pb.rpi, torch.tensor(prefix), torch.tensor([n] * 2), D ** -0.5,
                            custom_mask=mask2.to(torch.uint8), mask_indptr=indptr)
     assert_close_scaled(out_g.float().cpu().view(pb.T, Hq, D), want2, "graph replay with a new mask")
+
+    # EAGLE's overlapped plan: the replay prep ran with a stale mask, the worker hands the real one over after the
+    # draft through update_verify_buffers_to_fill_after_draft (eagle_worker_common.py:505-535)
+    mask3 = tree_mask()
+    fb.spec_info = SimpleNamespace(draft_token_num=n, custom_mask=torch.ones_like(mask3).cuda())      # stale
+    be.init_forward_metadata_out_graph(fb)
+    be.update_verify_buffers_to_fill_after_draft(SimpleNamespace(draft_token_num=n, custom_mask=mask3.cuda()), pb.bs)
+    graph.replay()
+    torch.cuda.synchronize()
+    want3 = ref.extend_ref(pb.q, pb.kp, pb.vp, pb.rtt, pb.rpi, torch.tensor(prefix), torch.tensor([n] * 2), D ** -0.5,
+                           custom_mask=mask3.to(torch.uint8), mask_indptr=indptr)
+    assert_close_scaled(out_g.float().cpu().view(pb.T, Hq, D), want3, "mask refreshed after the draft")
