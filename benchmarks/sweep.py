@@ -254,6 +254,14 @@ def main():
         emit(rope_store_case("decode rope+store 64 rows 8B bf16", 64, 32, 8, 128, bf, a.iters))
         emit(rope_store_case("cfg5 rope+store 131072 rows 8B bf16", 131072, 32, 8, 128, bf, a.iters))
         emit(rope_store_case("cfg5 rope+store 131072 rows 8B fp8", 131072, 32, 8, 128, e4, a.iters))
+    if a.only == "d256":
+        it = max(3, a.iters // 10)
+        emit(extend_case("D256 gemma-2 heads (16/8) 8 req x (16K shared prefix + 1K), tcgen05 one-tile", 8, 16384, 1024, 16, 8,
+                         256, it))
+        emit(extend_case("D256 gemma-2 heads (16/8) 8 req x (16K shared prefix + 1K), FP8-e4m3 pool", 8, 16384, 1024, 16, 8,
+                         256, it, pool_dtype=e4))
+        emit(extend_case("D256 gemma-2 heads (16/8) 8 req x (16K shared prefix + 1K), FP8-e5m2 pool", 8, 16384, 1024, 16, 8,
+                         256, it, pool_dtype=torch.float8_e5m2))
     if a.only in ("", "extend"):
         it = max(3, a.iters // 10)
         emit(extend_case("cfg5/16 8 req x (16K shared prefix + 1K)", 8, 16384, 1024, 32, 8, 128, it))
@@ -274,6 +282,8 @@ def main():
                          shared=False, tree_mask=True, kernel=1))
         emit(extend_case("D256 gemma-2 heads (16/8) 8 req x (16K shared prefix + 1K), tcgen05 one-tile", 8, 16384, 1024, 16, 8,
                          256, it))
+        emit(extend_case("D256 gemma-2 heads (16/8) 8 req x (16K shared prefix + 1K), FP8-e4m3 pool", 8, 16384, 1024, 16, 8,
+                         256, it, pool_dtype=e4))
         emit(extend_case("D256 gemma-2 heads (16/8), generic kernel (CUDA cores), 1 req x (4K + 256)", 1, 4096, 256, 16, 8,
                          256, 3, kernel=1))
         emit(extend_case("D64 qwen2.5-0.5b heads 8 req x (16K shared prefix + 1K)", 8, 16384, 1024, 14, 2, 64, it))

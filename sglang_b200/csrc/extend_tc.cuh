@@ -168,7 +168,7 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
                  const __grid_constant__ CUtensorMap tm_v) {
   static_assert(!(kTma && kFp8), "the FP8 producers widen bytes themselves");
   static_assert(!(kTma && kOneTile), "the one-tile instance keeps the row gather");
-  static_assert(kHD != 256 || (kOneTile && !kFp8), "D = 256 exists as the one-tile, 16-bit-pool instance only");
+  static_assert(kHD != 256 || kOneTile, "D = 256 exists as the one-tile instance only");
   constexpr int kNT = kOneTile ? 1 : tc::kQTiles;           // query tiles of this instance
   using namespace tc;
   using namespace ptx;
@@ -302,7 +302,6 @@ bool extend_fast_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype
   if (dqk != dv || (dqk != 128 && dqk != 64 && dqk != 256)) return false;
   if (group < 1 || group > 128) return false;
   if (q_dtype != B200_BF16 && q_dtype != B200_F16) return false;
-  if (dqk == 256) return kv_dtype == q_dtype;          // D = 256: 16-bit pools (one-tile instance)
   return kv_dtype == q_dtype || kv_dtype == B200_FP8_E4M3 || kv_dtype == B200_FP8_E5M2;
 }
 
@@ -419,12 +418,10 @@ int launch_extend_fast_d(const ExtendParams& p, const b200_extend_args& a, cudaS
 
 template <typename QT, bool kFp8>
 int launch_extend_fast_q(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
-  if constexpr (!kFp8) {
-    if (p.head_dim_qk == 256) {
-      const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr || p.custom_mask != nullptr;
-      return opts ? launch_extend_fast_t<QT, false, true, 256, false, true>(p, a, stream)
-                  : launch_extend_fast_t<QT, false, false, 256, false, true>(p, a, stream);
-    }
+  if (p.head_dim_qk == 256) {
+    const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr || p.custom_mask != nullptr;
+    return opts ? launch_extend_fast_t<QT, kFp8, true, 256, false, true>(p, a, stream)
+                : launch_extend_fast_t<QT, kFp8, false, 256, false, true>(p, a, stream);
   }
   return p.head_dim_qk == 64 ? launch_extend_fast_d<QT, kFp8, 64>(p, a, stream)
                              : launch_extend_fast_d<QT, kFp8, 128>(p, a, stream);

@@ -61,7 +61,8 @@ def test_pure_host_queries_work_without_gpu():
         assert ops.extend_fast_supported(D, D, 7, torch.float16, torch.float8_e4m3fn)
         assert ops.extend_block_q(D, D, 4, torch.bfloat16, torch.bfloat16) == 64   # 2 tiles x 128 / group tokens
     assert ops.extend_fast_supported(256, 256, 4, torch.bfloat16, torch.bfloat16)        # one-tile D 256 instance
-    assert not ops.extend_fast_supported(256, 256, 4, torch.bfloat16, torch.float8_e4m3fn)
+    assert ops.extend_fast_supported(256, 256, 4, torch.bfloat16, torch.float8_e4m3fn)   # ... also with FP8 pools
+    assert ops.extend_fast_supported(256, 256, 4, torch.float16, torch.float8_e5m2)
     assert ops.extend_block_q(256, 256, 4, torch.bfloat16, torch.bfloat16) == 32         # one 128-row tile
     assert ops.extend_block_q_one_tile(128, 128, 4, torch.bfloat16, torch.bfloat16) == 32
     assert ops.decode_fast_supported(128, 128, 4, torch.bfloat16, torch.float8_e5m2)

@@ -87,7 +87,7 @@ SHAPES = [
     (16, 4, 64, [300, 0, 127], [260, 129, 1], 16),     # D 64, group 4: several q tiles and kv blocks, page 16
     (4, 4, 64, [200], [400], 1),                       # D 64 MHA: 128 tokens per q tile
     (4, 4, 80, [10, 0], [33, 17], 1),                  # odd head dim -> generic
-    (4, 4, 256, [33], [70], 32),                       # D 256 MHA -> one-tile tcgen05 instance (16-bit pools)
+    (4, 4, 256, [33], [70], 32),                       # D 256 MHA -> one-tile tcgen05 instance (16-bit and FP8 pools)
     (8, 2, 256, [300, 0, 127], [260, 129, 1], 1),      # D 256, group 4 (Gemma-like): several q tiles / kv blocks
     (16, 8, 256, [1000], [200], 16),                   # D 256, group 2, page 16
     (16, 1, 128, [100], [150], 1),                     # group 16
@@ -171,7 +171,8 @@ def test_fast_path_covers_d256_16bit_pools():
 
     assert ops.extend_fast_supported(256, 256, 2, torch.bfloat16, torch.bfloat16)
     assert ops.extend_fast_supported(256, 256, 4, torch.float16, torch.float16)
-    assert not ops.extend_fast_supported(256, 256, 2, torch.bfloat16, torch.float8_e4m3fn)
+    assert ops.extend_fast_supported(256, 256, 2, torch.bfloat16, torch.float8_e4m3fn)     # FP8 pools: same instance
+    assert ops.extend_fast_supported(256, 256, 2, torch.float16, torch.float8_e5m2)
     assert ops.extend_block_q(256, 256, 2, torch.bfloat16, torch.bfloat16) == 64      # one 128-row tile per item
 
 
