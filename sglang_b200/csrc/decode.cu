@@ -40,6 +40,7 @@ __device__ __forceinline__ int64_t attended_len(const void* seq_lens, int is_i64
 }
 
 constexpr int kPlanThreads = 1024;
+constexpr int kPlanCache = 2048;     // requests whose lengths are kept in shared memory by the planner
 
 __device__ __forceinline__ int64_t block_sum_i64(int64_t v, int64_t* s_red) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -66,13 +67,23 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanPar
   __shared__ int64_t s_cost[32], s_cand[32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int bs = p.batch_size;
+  // The attended lengths are read once into shared memory as 32-bit values (negative -> 0): the search below evaluates
+  // items() ~10 times per warp, and 64-bit divisions on re-loaded int64 lengths made this kernel 19 us for 64 requests.
+  __shared__ uint32_t s_len[kPlanCache];
+  auto len_at = [&](int r) -> uint32_t {
+    if (r < kPlanCache) return s_len[r];
+    const int64_t L = attended_len(p.seq_lens, p.seq_lens_is_i64, r, p.window_keys);
+    return L > 0 ? (uint32_t)(L < 0x7fffffff ? L : 0x7fffffff) : 0u;
+  };
 
   int64_t local = 0;
   for (int r = tid; r < bs; r += kPlanThreads) {
     const int64_t L = attended_len(p.seq_lens, p.seq_lens_is_i64, r, p.window_keys);
-    local += L > 0 ? L : 0;
+    const uint32_t l32 = L > 0 ? (uint32_t)(L < 0x7fffffff ? L : 0x7fffffff) : 0u;
+    if (r < kPlanCache) s_len[r] = l32;
+    local += l32;
   }
-  const int64_t total = block_sum_i64(local, s_red);
+  const int64_t total = block_sum_i64(local, s_red);      // (its barriers also publish s_len)
 
   // Candidate m = warp + 1 "rounds": the smallest chunk (multiple of 16 tokens, >= min_chunk) whose item
   // count  items(chunk) = G * sum_r ceil(L_r / chunk)  fits m * num_ctas, found by bisection (items() is
@@ -80,37 +91,31 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanPar
   // to fewer rounds.  Every warp works alone (no block barrier inside the search).
   {
     const int m = warp + 1;
-    int64_t maxl = 0;
-    for (int r = lane; r < bs; r += 32) {
-      const int64_t L = attended_len(p.seq_lens, p.seq_lens_is_i64, r, p.window_keys);
-      maxl = L > maxl ? L : maxl;
-    }
+    uint32_t maxl = 0;
+    for (int r = lane; r < bs; r += 32) maxl = max(maxl, len_at(r));
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const int64_t t = __shfl_xor_sync(0xffffffffu, maxl, o);
-      maxl = t > maxl ? t : maxl;
-    }
-    auto items = [&](int64_t chunk) -> int64_t {
+    for (int o = 16; o > 0; o >>= 1) maxl = max(maxl, __shfl_xor_sync(0xffffffffu, maxl, o));
+    auto items = [&](uint32_t chunk) -> int64_t {          // chunk <= 2^31: L + chunk - 1 fits 32 bits
       int64_t n = 0;
       for (int r = lane; r < bs; r += 32) {
-        const int64_t L = attended_len(p.seq_lens, p.seq_lens_is_i64, r, p.window_keys);
+        const uint32_t L = len_at(r);
         if (L > 0) n += (L + chunk - 1) / chunk;
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
       return n * p.num_kv_heads;
     };
-    const int64_t u_min = (p.min_chunk + 15) / 16;
-    int64_t u_max = (maxl + 15) / 16;
+    const uint32_t u_min = (uint32_t)(p.min_chunk + 15) / 16;
+    uint32_t u_max = (uint32_t)(((int64_t)maxl + 15) / 16);
     if (u_max < u_min) u_max = u_min;
     const int64_t cap = (int64_t)m * p.num_ctas;
-    int64_t lo = u_min, hi = u_max;            // smallest u in [u_min, u_max] with items(16 u) <= cap, else u_max
+    uint32_t lo = u_min, hi = u_max;           // smallest u in [u_min, u_max] with items(16 u) <= cap, else u_max
     while (lo < hi) {
-      const int64_t mid = (lo + hi) >> 1;
+      const uint32_t mid = (lo + hi) >> 1;
       if (items(16 * mid) <= cap) hi = mid; else lo = mid + 1;
     }
-    const int64_t chunk = 16 * lo;
-    const int64_t rounds = (items(chunk) + p.num_ctas - 1) / p.num_ctas;
+    const int64_t chunk = 16 * (int64_t)lo;
+    const int64_t rounds = (items((uint32_t)chunk) + p.num_ctas - 1) / p.num_ctas;
     if (lane == 0) {
       s_cost[warp] = (m <= p.waves) ? rounds * (chunk + p.min_chunk / 4) : (int64_t(1) << 62);
       s_cand[warp] = chunk;
@@ -143,8 +148,8 @@ __global__ void __launch_bounds__(kPlanThreads) decode_plan_kernel(const PlanPar
     const int r = base + tid;
     int32_t n = 0;
     if (r < bs) {
-      const int64_t L = attended_len(p.seq_lens, p.seq_lens_is_i64, r, p.window_keys);
-      n = L > 0 ? (int32_t)((L + chunk - 1) / chunk) : 0;
+      const uint32_t L = len_at(r);
+      n = L > 0 ? (int32_t)((L + (uint32_t)chunk - 1) / (uint32_t)chunk) : 0;
     }
     int32_t inc = n;
 #pragma unroll
