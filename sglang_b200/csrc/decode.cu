@@ -443,7 +443,8 @@ bool decode_hg_shape_ok(int hq, int hkv, int dqk, int dv, int q_dtype, int kv_dt
 
 extern "C" int b200attn_decode_ctas_per_sm(int32_t head_dim, int32_t kv_dtype) {
   const int a = b200::decode_fast_ctas_per_sm(head_dim, kv_dtype);
-  const int b = b200::decode_hg_enabled() && (head_dim == 64 || head_dim == 128 || head_dim == 256)
+  const int b = b200::decode_hg_enabled() && (head_dim == 64 || head_dim == 128 || head_dim == 256 || head_dim == 80 ||
+                                              head_dim == 96 || head_dim == 112)
                     ? b200::decode_hg_ctas_per_sm(head_dim, kv_dtype) : 0;
   return a > b ? a : b;
 }

@@ -40,8 +40,15 @@ struct HgCfg {
   // D = 64 FP8 pools: a head row is 64 bytes (4 chunks), the 4-head slice 256 bytes = HALF a warp's cp.async, so one
   // copy instruction covers two tokens and the swizzle runs over chunk indices that span two heads
   static constexpr bool kHalfWarpTok = kTokB == 256;
-  static_assert(kCpr % 8 == 0 || (kCpr == 4 && kFp8), "head rows: whole 128-byte lines, or 64-byte FP8 rows");
-  static_assert(kTokB % 512 == 0 || kHalfWarpTok, "a token slice must be whole (or exactly half) full-warp copies");
+  // D = 80 / 96 / 112 with 16-bit pools (Phi-class heads): rows of 160 / 192 / 224 bytes -- the 4-head slice is still
+  // contiguous and a multiple of 128 bytes, so the gather walks it as a flat list of 16-byte chunks (kFlatGather) and
+  // a head's first chunk goes through the swizzle XOR like the 64-byte FP8 rows
+  static constexpr bool kFlatGather = !kFp8 && kCpr % 8 != 0;
+  static constexpr int kTokChunks = kTokB / 16;
+  static_assert(kCpr % 8 == 0 || (kCpr == 4 && kFp8) || (kFlatGather && kCpr % 2 == 0 && kTokChunks % 8 == 0),
+                "head rows: whole 128-byte lines, 64-byte FP8 rows, or 16-bit rows of a multiple of 32 bytes");
+  static_assert(kTokB % 512 == 0 || kHalfWarpTok || (kFlatGather && (kTokPerWarp * kTokChunks) % 32 == 0),
+                "a token slice must be whole (or exactly half) full-warp copies, or a flat chunk list");
   static_assert(!kHalfWarpTok || kTokPerWarp % 2 == 0, "half-warp copies take tokens in pairs");
 };
 
@@ -148,6 +155,18 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
         for (int k = 0; k < C::kTokPerWarp / 2; ++k) {                     // lanes 0-15: one token, 16-31: the next
           const int tok = warp * C::kTokPerWarp + 2 * k + (lane >> 4);
           const int ch = lane & 15;                                        // 16-byte chunk of the 4-head slice
+          const int64_t slot = __shfl_sync(0xffffffffu, pt_cur, (T & 1) * 16 + tok);
+          const bool valid = T * kTileTok + tok < n_tok;
+          const uint32_t off = tok * C::kTokB + ((ch ^ (tok & 7)) << 4);
+          cp_async_16(kst + off, kc + slot * k_slot_b + ch * 16, valid);
+          cp_async_16(vst + off, vc + slot * v_slot_b + ch * 16, valid);
+        }
+      } else if constexpr (C::kFlatGather) {
+#pragma unroll
+        for (int i = 0; i < C::kTokPerWarp * C::kTokChunks / 32; ++i) {    // this warp's tokens as one list of chunks
+          const int f = i * 32 + lane;
+          const int t = f / C::kTokChunks, ch = f - t * C::kTokChunks;
+          const int tok = warp * C::kTokPerWarp + t;
           const int64_t slot = __shfl_sync(0xffffffffu, pt_cur, (T & 1) * 16 + tok);
           const bool valid = T * kTileTok + tok < n_tok;
           const uint32_t off = tok * C::kTokB + ((ch ^ (tok & 7)) << 4);
@@ -368,7 +387,9 @@ __global__ void __launch_bounds__(kHG* kWarp, HgCfg<D, KV>::kMinBlocks) decode_h
 bool decode_hg_dims_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype) {
   if (decode_fast_supported(dqk, dv, group, q_dtype, kv_dtype)) return true;
   const bool fp8 = kv_dtype == B200_FP8_E4M3 || kv_dtype == B200_FP8_E5M2;
-  return fp8 && dqk == 64 && dv == 64 && group >= 1 && group <= 16 && (q_dtype == B200_BF16 || q_dtype == B200_F16);
+  if (dqk != dv || group < 1 || group > 16 || (q_dtype != B200_BF16 && q_dtype != B200_F16)) return false;
+  if (fp8) return dqk == 64;
+  return kv_dtype == q_dtype && (dqk == 80 || dqk == 96 || dqk == 112);     // Phi-class heads, 16-bit pools
 }
 
 bool decode_hg_supported(const DecodeParams& p, int q_dtype, int kv_dtype) {
@@ -390,8 +411,13 @@ int launch_decode_hg_inst(const DecodeParams& p, int num_ctas, cudaStream_t stre
   B200_CHECK_CUDA(set_max_dynamic_smem(kern, C::kCtaSmem, configured));
   B200_CHECK_CUDA(launch_pdl(kern, dim3(num_ctas), dim3(kHG * kWarp), C::kCtaSmem, stream, p));
   B200_CHECK_CUDA(cudaGetLastError());
-  B200_CHECK_CUDA(launch_pdl(decode_merge_fast_kernel<QT, D>, dim3(p.batch_size * p.num_q_heads), dim3(kFastWarps * kWarp), 0,
-                             stream, p));
+  if constexpr (D % 64 == 0) {
+    B200_CHECK_CUDA(launch_pdl(decode_merge_fast_kernel<QT, D>, dim3(p.batch_size * p.num_q_heads), dim3(kFastWarps * kWarp), 0,
+                               stream, p));
+  } else {          // D = 80 / 96 / 112: the generic split merge (same partial format)
+    const int64_t rows = (int64_t)p.batch_size * p.num_q_heads;
+    decode_merge_kernel<QT><<<(unsigned)((rows + kMergeWarps - 1) / kMergeWarps), kMergeWarps * kWarp, 0, stream>>>(p);
+  }
   B200_CHECK_CUDA(cudaGetLastError());
   return B200_OK;
 }
@@ -416,6 +442,9 @@ int launch_decode_hg_q(const DecodeParams& p, int kv_dtype, int num_ctas, cudaSt
   } else {
     if (D == 64) return launch_decode_hg_d<64, kSame, QT>(p, num_ctas, stream);
     if (D == 128) return launch_decode_hg_d<128, kSame, QT>(p, num_ctas, stream);
+    if (D == 80) return launch_decode_hg_d<80, kSame, QT>(p, num_ctas, stream);
+    if (D == 96) return launch_decode_hg_d<96, kSame, QT>(p, num_ctas, stream);
+    if (D == 112) return launch_decode_hg_d<112, kSame, QT>(p, num_ctas, stream);
   }
   set_error("decode head-group: no instance for D=%d kv=%d", D, kv_dtype);
   return B200_EINVAL;
@@ -430,7 +459,8 @@ int launch_decode_hg(const DecodeParams& p, int q_dtype, int kv_dtype, int num_c
 int decode_hg_ctas_per_sm(int head_dim, int kv_dtype) {
   const bool fp8 = kv_dtype == B200_FP8_E4M3 || kv_dtype == B200_FP8_E5M2;
   const int stage = 2 * kTileTok * kHG * head_dim * (fp8 ? 1 : 2);
-  const int smem = (stage <= 16 * 1024 ? 4 : 3) * stage;
+  const int stages = stage <= 16 * 1024 ? 4 : 3;
+  const int smem = stages * stage + 16 * stages;          // HgCfg::kCtaSmem
   return smem > 110 * 1024 ? 1 : (smem <= 36 * 1024 ? B200_HG_SMALL_BLOCKS : (smem <= 72 * 1024 ? 3 : 2));
 }
 

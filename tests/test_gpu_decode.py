@@ -138,6 +138,30 @@ def test_decode_d64_fp8_head_group_kernel(shape, dtype, pool_dtype):
     assert float((got - gen).abs().max()) <= 2e-2
 
 
+ODD_D_SHAPES = [
+    # bs, Hq, Hkv, D, lens, page
+    (3, 32, 32, 96, [1, 17, 1300], 1),         # Phi-3-mini heads (MHA, D 96)
+    (2, 32, 32, 80, [515, 64], 16),            # Phi-2 heads (D 80), paged
+    (2, 16, 4, 112, [300, 129], 1),            # D 112, group 4
+    (2, 64, 4, 96, [700, 33], 1),              # group 16 (upper MMA rows)
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "f16"])
+@pytest.mark.parametrize("shape", ODD_D_SHAPES, ids=[f"h{s[1]}_{s[2]}_d{s[3]}_p{s[5]}" for s in ODD_D_SHAPES])
+def test_decode_d80_d96_d112_head_group_kernel(shape, dtype):
+    """Head dims 80 / 96 / 112 (rows of 160 / 192 / 224 bytes) with 16-bit pools on the tensor-core head-group kernel:
+    flat chunk gather, swizzle across heads, generic split merge.  KERNEL_FAST refuses shapes without an instance."""
+    bs, Hq, Hkv, D, lens, page = shape
+    q, kp, vp, rtt, rpi, seq = _random_problem(bs, Hq, Hkv, D, lens, page, dtype, dtype, seed=D + bs)
+    want = ref.decode_ref(q, kp, vp, rtt, rpi, seq, D**-0.5, kv_dtype=dtype)
+    for kernel, chunk in ((2, 0), (0, 0), (2, 64)):
+        got, _ = _run_ops_decode(q, kp, vp, rtt, rpi, seq, D**-0.5, dtype, kernel=kernel, fixed_chunk=chunk)
+        assert_close_scaled(got, want, f"kernel {kernel} chunk {chunk}")
+    gen, _ = _run_ops_decode(q, kp, vp, rtt, rpi, seq, D**-0.5, dtype, kernel=KERNELS["generic"])
+    assert float((got - gen).abs().max()) <= 2e-2
+
+
 def test_decode_d64_fp8_needs_four_kv_heads_for_the_fast_path():
     """Hkv not a multiple of 4 (Qwen2.5-0.5B: 2 kv heads) keeps the CUDA-core kernel for D = 64 FP8 pools: AUTO works,
     FAST refuses loudly."""
