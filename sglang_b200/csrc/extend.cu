@@ -164,6 +164,9 @@ struct ExtendParams {
   int32_t num_splits;
   float* split_o;
   float* split_lse;
+  // 16-byte chunks of a real Q/K/V row (head_dim / 8).  Head dims 80 / 96 / 112 run on the D = 128 one-tile instance
+  // with the remaining chunks of every tile row zero-filled (exact: the padding multiplies by zero).
+  int32_t d_chunks;
 };
 
 constexpr int kSplitMinBlocks = 4;   // a split part keeps at least this many kv blocks (the device trims num_splits per item)
@@ -407,6 +410,7 @@ extern "C" int b200attn_extend(const b200_extend_args* a, b200_stream_t stream_)
   p.custom_mask = a->custom_mask; p.mask_indptr = a->mask_indptr; p.mask_skip_prefix = a->mask_skip_prefix;
   p.kv_e5m2 = a->kv_dtype == B200_FP8_E5M2;
   p.num_splits = 1; p.split_o = nullptr; p.split_lse = nullptr;
+  p.d_chunks = a->head_dim_qk / 8;
   p.tma_rows = 0;
   p.pool_slots = a->pool_slots > 0 && a->pool_slots < 0x7fffffff ? (int32_t)a->pool_slots : 0;
   B200_CHECK_ARG(a->custom_mask == nullptr || a->mask_indptr != nullptr, "extend: custom_mask needs mask_indptr");

@@ -298,7 +298,12 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
 }
 
 
+// head dims that run zero-padded on the D = 128 one-tile instance (16-bit pools)
+bool extend_padded_dim(int d) { return d == 80 || d == 96 || d == 112; }
+
 bool extend_fast_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype) {
+  if (dqk == dv && extend_padded_dim(dqk))
+    return group >= 1 && group <= 128 && (q_dtype == B200_BF16 || q_dtype == B200_F16) && kv_dtype == q_dtype;
   if (dqk != dv || (dqk != 128 && dqk != 64 && dqk != 256)) return false;
   if (group < 1 || group > 128) return false;
   if (q_dtype != B200_BF16 && q_dtype != B200_F16) return false;
@@ -306,7 +311,9 @@ bool extend_fast_supported(int dqk, int dv, int group, int q_dtype, int kv_dtype
 }
 
 // query tokens per work item (two 128-row tiles of 128/group tokens each; D = 256 has the one-tile instance only)
-int extend_fast_block_q(int group, int head_dim) { return (head_dim == 256 ? 1 : tc::kQTiles) * (128 / group); }
+int extend_fast_block_q(int group, int head_dim) {
+  return ((head_dim == 256 || extend_padded_dim(head_dim)) ? 1 : tc::kQTiles) * (128 / group);
+}
 // ... or one 128-row tile (the kOneTile instance): the host picks it when no request extends by more tokens
 int extend_fast_block_q_one_tile(int group) { return 128 / group; }
 
@@ -404,7 +411,7 @@ int launch_extend_fast_t(const ExtendParams& p_in, const b200_extend_args& a, cu
 template <typename QT, bool kFp8, int kHD>
 int launch_extend_fast_d(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {
   const bool opts = p.window_keys > 0 || p.logit_cap > 0.f || p.sinks != nullptr || p.custom_mask != nullptr;
-  if (a.block_q == extend_fast_block_q_one_tile(p.group))          // the plan holds one-tile items
+  if (a.block_q == extend_fast_block_q_one_tile(p.group) || extend_padded_dim(p.head_dim_qk))   // one-tile items
     return opts ? launch_extend_fast_t<QT, kFp8, true, kHD, false, true>(p, a, stream)
                 : launch_extend_fast_t<QT, kFp8, false, kHD, false, true>(p, a, stream);
   if constexpr (!kFp8) {
@@ -424,7 +431,7 @@ int launch_extend_fast_q(const ExtendParams& p, const b200_extend_args& a, cudaS
                 : launch_extend_fast_t<QT, kFp8, false, 256, false, true>(p, a, stream);
   }
   return p.head_dim_qk == 64 ? launch_extend_fast_d<QT, kFp8, 64>(p, a, stream)
-                             : launch_extend_fast_d<QT, kFp8, 128>(p, a, stream);
+                             : launch_extend_fast_d<QT, kFp8, 128>(p, a, stream);     // 128, and 80 / 96 / 112 padded
 }
 
 int launch_extend_fast(const ExtendParams& p, const b200_extend_args& a, cudaStream_t stream) {

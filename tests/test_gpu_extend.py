@@ -86,7 +86,7 @@ SHAPES = [
     (14, 2, 64, [512, 512], [63, 5], 1),               # Qwen2.5-0.5B heads (group 7) -> kHD = 64 tcgen05 instance
     (16, 4, 64, [300, 0, 127], [260, 129, 1], 16),     # D 64, group 4: several q tiles and kv blocks, page 16
     (4, 4, 64, [200], [400], 1),                       # D 64 MHA: 128 tokens per q tile
-    (4, 4, 80, [10, 0], [33, 17], 1),                  # odd head dim -> generic
+    (4, 4, 80, [10, 0], [33, 17], 1),                  # D 80 -> padded onto the D 128 one-tile instance (16-bit pools)
     (4, 4, 256, [33], [70], 32),                       # D 256 MHA -> one-tile tcgen05 instance (16-bit and FP8 pools)
     (8, 2, 256, [300, 0, 127], [260, 129, 1], 1),      # D 256, group 4 (Gemma-like): several q tiles / kv blocks
     (16, 8, 256, [1000], [200], 16),                   # D 256, group 2, page 16
@@ -182,7 +182,9 @@ def test_fast_path_covers_d64_and_d128():
     for D in (64, 128):
         for kv in (torch.bfloat16, torch.float8_e4m3fn):
             assert ops.extend_fast_supported(D, D, 4, torch.bfloat16, kv)
-    assert not ops.extend_fast_supported(80, 80, 4, torch.bfloat16, torch.bfloat16)
+    assert ops.extend_fast_supported(80, 80, 4, torch.bfloat16, torch.bfloat16)           # padded onto the D 128 tile
+    assert not ops.extend_fast_supported(80, 80, 4, torch.bfloat16, torch.float8_e4m3fn)  # ... 16-bit pools only
+    assert not ops.extend_fast_supported(72, 72, 4, torch.bfloat16, torch.bfloat16)
     assert not ops.extend_fast_supported(128, 64, 4, torch.bfloat16, torch.bfloat16)
 
 

@@ -245,3 +245,39 @@ def test_backend_verify_picks_split_kv_and_matches_oracle():
     want3 = ref.extend_ref(pb.q, pb.kp, pb.vp, pb.rtt, pb.rpi, torch.tensor(prefix), torch.tensor([n] * 2), D ** -0.5,
                            custom_mask=mask3.to(torch.uint8), mask_indptr=indptr)
     assert_close_scaled(out_g.float().cpu().view(pb.T, Hq, D), want3, "mask refreshed after the draft")
+
+
+PADDED_SHAPES = [
+    # Hq, Hkv, D, prefix, extend, page
+    (32, 32, 96, [0, 700, 130], [300, 260, 1], 1),       # Phi-3-mini heads (MHA): several q tiles
+    (32, 32, 80, [1500], [600], 16),                     # Phi-2 heads, long prefix, paged
+    (16, 4, 112, [5, 0], [250, 129], 1),                 # D 112, group 4
+    (8, 1, 96, [2100, 40], [18, 5], 1),                  # group 8, short extends
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "f16"])
+@pytest.mark.parametrize("shape", PADDED_SHAPES, ids=[f"h{s[0]}_{s[1]}_d{s[2]}_p{s[5]}" for s in PADDED_SHAPES])
+def test_extend_d80_d96_d112_on_the_padded_d128_tile(shape, dtype):
+    """Head dims 80 / 96 / 112 (16-bit pools) run on the tcgen05 D = 128 one-tile instance with zero-filled padding;
+    KERNEL_FAST (2) refuses shapes without a tensor-core instance.  Also with split-KV, options and LSE."""
+    from sglang_b200 import ops
+    from test_gpu_extend import run_ops_extend
+
+    Hq, Hkv, D, prefix, extend, page = shape
+    assert ops.extend_fast_supported(D, D, Hq // Hkv, dtype, dtype)
+    assert ops.extend_block_q(D, D, Hq // Hkv, dtype, dtype) == 128 // (Hq // Hkv)
+    q, kp, vp, rtt, rpi, pre, ext = make_extend_problem(Hq, Hkv, D, prefix, extend, page, dtype, dtype, seed=D)
+    scale = D**-0.5
+    want, want_lse = ref.extend_ref(q, kp, vp, rtt, rpi, pre, ext, scale, kv_dtype=dtype, want_lse=True)
+    got, lse = run_ops_extend(q, kp, vp, rtt, rpi, pre, ext, scale, dtype, kernel=2, page_size=page, want_lse=True)
+    assert_close_scaled(got, want, "fast")
+    assert float((lse.cpu() - want_lse).abs().max()) <= ATOL
+    got3, lse3 = _run(q, kp, vp, rtt, rpi, pre, ext, scale, dtype, 3, page_size=page)
+    assert_close_scaled(got3, want, "3 splits")
+    assert float((lse3 - want_lse).abs().max()) <= ATOL
+    sinks = torch.randn(Hq, generator=torch.Generator().manual_seed(2)) * 2
+    kw = dict(window_keys=200, logit_cap=40.0, sinks=sinks)
+    want_o = ref.extend_ref(q, kp, vp, rtt, rpi, pre, ext, scale, kv_dtype=dtype, **kw)
+    got_o, _ = _run(q, kp, vp, rtt, rpi, pre, ext, scale, dtype, 1, page_size=page, **dict(kw))
+    assert_close_scaled(got_o, want_o, "window + cap + sinks")
