@@ -300,7 +300,7 @@ def test_backend_short_extend_plans_one_tile_items():
         assert_close_scaled(out.float().cpu().view_as(want), want, f"extend lens {ext}")
 
 
-@pytest.mark.parametrize("Hq,Hkv,D", [(32, 8, 128), (64, 8, 64), (8, 2, 128), (16, 8, 256)])
+@pytest.mark.parametrize("Hq,Hkv,D", [(32, 8, 128), (64, 8, 64), (8, 2, 128), (16, 8, 256), (32, 32, 96), (16, 4, 80)])
 def test_backend_hybrid_sliding_window(Hq, Hkv, D):
     """A hybrid model: layer 0 sliding window (W = 127 -> 128 keys) with sinks, layer 1 full attention; decode and
     extend through the plugin API, one metadata call per forward (two decode plans)."""
