@@ -45,7 +45,10 @@ class _Finder(importlib.abc.MetaPathFinder, importlib.abc.Loader):
         return m
 
     def exec_module(self, module):
-        pass
+        if module.__name__ == "sgl_kernel.utils":
+            # a capability probe, not a kernel: the reference's Triton backend asks it at construction
+            # (triton_backend.py:231); without the wheel there is no PDL launch path
+            module.is_arch_support_pdl = lambda: False
 
 
 sys.meta_path.append(_Finder())

@@ -157,6 +157,9 @@ class B200AttnBackend(_Base):
                                                              self.kv_dtype, self.extend_kernel)
         self._ext_block_q = self._extend_block_q      # block_q of the current forward's plan
         self._ext_splits, self._ext_split_ws = 1, None      # split-KV choice of the current forward (one-tile plans)
+        # > 0: this instance is step (offset - 1) of a multi-step draft decode (see B200MultiStepDraftBackend)
+        self.draft_step_offset = 0
+        self._draft_seq_lens = {}
         self._ext_short = False                               # the host knows that no request extends by more than one tile
         self.num_draft_tokens = _spec_num_draft_tokens(model_runner)
         self.forward_metadata = None
@@ -331,7 +334,7 @@ class B200AttnBackend(_Base):
         if mode.is_idle():
             return
         if mode.is_decode():
-            seq_lens = forward_batch.seq_lens[: forward_batch.batch_size]
+            seq_lens = self._decode_seq_lens(forward_batch, forward_batch.batch_size, refresh=True)
             ops.decode_plan(self.decode_ws, seq_lens, self.num_kv_head, waves=self.DECODE_WAVES,
                             items_per_chunk=self._decode_items)
             if self.decode_ws_swa is not None:
@@ -347,6 +350,24 @@ class B200AttnBackend(_Base):
                             req_to_token=self.req_to_token_pool.req_to_token if paged else None,
                             req_pool_indices=forward_batch.req_pool_indices[: ext.shape[0]] if paged else None,
                             extend_prefix_lens=pre if paged else None)
+
+    def _decode_seq_lens(self, forward_batch, bs: int, refresh: bool = False):
+        """The lengths a decode step attends.  A plain backend reads `forward_batch.seq_lens`.  Step i of a multi-step
+        EAGLE draft (B200MultiStepDraftBackend) attends the prefix plus the i + 1 tokens drafted so far, whose slots
+        the worker has written behind the prefix in `req_to_token` (cache_locs.py:104-108 for topk 1), i.e.
+        `seq_lens + offset`: kept in a persistent buffer that the graph-recordable metadata hook refreshes."""
+        seq = forward_batch.seq_lens[:bs]
+        if self.draft_step_offset <= 0:
+            return seq
+        buf = self._draft_seq_lens.get(seq.dtype)
+        if buf is None or buf.numel() < bs:
+            if self._graph_state_frozen and buf is not None:
+                raise RuntimeError("b200 backend: draft-step length buffer would have to grow after a graph capture")
+            buf = torch.zeros(max(bs, self.max_bs), dtype=seq.dtype, device=seq.device)
+            self._draft_seq_lens[seq.dtype] = buf
+        if refresh:
+            torch.add(seq, self.draft_step_offset, out=buf[:bs])
+        return buf[:bs]
 
     def _pick_block_q(self, max_extend_len) -> int:
         """Query tokens per work item for this forward: one-tile items when the host knows that no request extends
@@ -407,6 +428,10 @@ class B200AttnBackend(_Base):
         pool = self.token_to_kv_pool
         idx = layer.layer_id - getattr(pool, "start_layer", 0)
         same = k.dtype == pool.dtype
+        if cache_loc.dim() != 1 or not cache_loc.is_contiguous():
+            # the EAGLE draft worker hands step i a strided row of its [steps, bs] slot table
+            # (eagle_worker_v2.py:563-632); set_kv_buffer takes any index tensor, the scatter kernel wants a dense one
+            cache_loc = cache_loc.reshape(-1).contiguous()
         ops.store_kv(
             k, v, pool.k_buffer[idx], pool.v_buffer[idx], cache_loc,
             cache_dtype=pool.dtype,
@@ -470,7 +495,7 @@ class B200AttnBackend(_Base):
             o.view(bs, layer.tp_q_head_num, layer.v_head_dim),
             k_buf, v_buf,
             self.req_to_token_pool.req_to_token,
-            forward_batch.req_pool_indices[:bs], forward_batch.seq_lens[:bs],
+            forward_batch.req_pool_indices[:bs], self._decode_seq_lens(forward_batch, bs),
             self.decode_ws_swa if window_keys else self.decode_ws, layer.scaling,
             kv_dtype=self.kv_dtype, k_scale=k_descale, v_scale=v_descale,
             logit_cap=self._logit_cap(layer), kernel=self.decode_kernel,
@@ -527,3 +552,81 @@ class B200AttnBackend(_Base):
 
     def support_triton(self):
         return True
+
+
+class B200MultiStepDraftBackend:
+    """EAGLE draft decode over several consecutive steps with `--speculative-eagle-topk 1` (chain drafting): the
+    reference wraps `speculative_num_steps - 1` per-step backends in one object that the draft worker initialises once
+    per draft and indexes per step (`TritonMultiStepDraftBackend`, triton_backend.py:1867-2042;
+    eagle_worker_v2.py:608-650 runs step i under `attn_backends[i]`).  The Triton version materialises per-step
+    kv_indices (`generate_draft_decode_kv_indices`); for topk 1 those are the request's `req_to_token` row up to
+    `seq_len + i + 1`, which this backend's decode kernels read directly -- so a step is a plain decode whose lengths
+    are `seq_lens + i + 1`.  Tree drafting (topk > 1) attends a non-contiguous slice of the row per branch and keeps
+    the Triton wrapper (sglang_b200.plugin)."""
+
+    needs_cpu_seq_lens: bool = False
+
+    def __init__(self, model_runner, topk: int, speculative_num_steps: int):
+        if int(topk) != 1:
+            raise ValueError("B200MultiStepDraftBackend covers chain drafting (topk 1) only")
+        self.topk = 1
+        self.speculative_num_steps = int(speculative_num_steps)
+        self.attn_backends = []
+        for i in range(self.speculative_num_steps - 1):
+            b = B200AttnBackend(model_runner, skip_prefill=True)
+            b.draft_step_offset = i + 1
+            self.attn_backends.append(b)
+        self.max_context_len = self.attn_backends[0].max_context_len if self.attn_backends else None
+        self.device = model_runner.device
+        self.req_to_token_pool = model_runner.req_to_token_pool
+        self.token_to_kv_pool = model_runner.token_to_kv_pool
+
+    @staticmethod
+    def _decode_view(forward_batch):
+        """The fields the per-step backends read, with the mode pinned to DECODE (forward_batch_info.py:1618-1656)."""
+        from types import SimpleNamespace
+
+        from .srt_mirror.forward_batch_info import ForwardMode as _FM
+
+        mode = forward_batch.forward_mode
+        try:                                   # inside an SGLang process the reference's own enum
+            from sglang.srt.model_executor.forward_batch_info import ForwardMode as _RealFM  # type: ignore
+
+            decode = _RealFM.DECODE
+        except Exception:
+            decode = _FM.DECODE
+        if mode.is_decode():
+            return forward_batch
+        return SimpleNamespace(
+            batch_size=forward_batch.batch_size, forward_mode=decode, actual_forward_mode=mode,
+            req_pool_indices=forward_batch.req_pool_indices, seq_lens=forward_batch.seq_lens,
+            seq_lens_sum=getattr(forward_batch, "seq_lens_sum", None),
+            seq_lens_cpu=getattr(forward_batch, "seq_lens_cpu", None),
+            out_cache_loc=getattr(forward_batch, "out_cache_loc", None),
+            positions=getattr(forward_batch, "positions", None), spec_info=getattr(forward_batch, "spec_info", None))
+
+    def init_forward_metadata(self, forward_batch):
+        view = self._decode_view(forward_batch)
+        for b in self.attn_backends:
+            b.init_forward_metadata(view)
+
+    def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
+        for b in self.attn_backends:
+            b.init_cuda_graph_state(max_bs, max_num_tokens)
+            n = max(int(max_bs), b.max_bs)
+            for dt in (torch.int32, torch.int64):       # the per-step length buffers a captured graph will hold
+                if dt not in b._draft_seq_lens or b._draft_seq_lens[dt].numel() < n:
+                    b._draft_seq_lens[dt] = torch.zeros(n, dtype=dt, device=self.device)
+
+    def init_forward_metadata_out_graph(self, forward_batch, in_capture: bool = False):
+        view = self._decode_view(forward_batch)
+        for b in self.attn_backends:
+            b.init_forward_metadata_out_graph(view, in_capture=in_capture)
+
+    def init_forward_metadata_in_graph(self, forward_batch):
+        view = self._decode_view(forward_batch)
+        for b in self.attn_backends:
+            b.init_forward_metadata_in_graph(view)
+
+    def get_cuda_graph_seq_len_fill_value(self):
+        return 1

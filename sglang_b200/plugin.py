@@ -36,3 +36,37 @@ def register() -> None:
         add_attention_backend_choices([BACKEND_NAME])
     except Exception:
         pass
+    _patch_draft_backend_factory()
+
+
+def _patch_draft_backend_factory() -> None:
+    """Speculative decoding: `DraftBackendFactory` resolves the draft model's backends through dicts that are local to
+    its methods (speculative/draft_utils.py:60-135), so a plugin backend name ends in "EAGLE is not supported in
+    attention backend b200".  Teach `_create_backend` the name: the draft-extend backend is a `B200AttnBackend`, the
+    multi-step draft-decode backend is `B200MultiStepDraftBackend` for chain drafting (topk 1) and the reference's own
+    Triton wrapper for tree drafting (its per-branch kv indices are not a prefix of the `req_to_token` row)."""
+    try:
+        from sglang.srt.speculative.draft_utils import DraftBackendFactory  # type: ignore
+    except Exception:
+        return
+    if getattr(DraftBackendFactory, "_b200_patched", False):
+        return
+    original = DraftBackendFactory._create_backend
+
+    def _create_backend(self, backend_name, backend_map, error_template):
+        backend_type = self.draft_attn_backend or getattr(self.server_args, backend_name, None)
+        if backend_type is None:
+            backend_type = self.server_args.attention_backend
+        if backend_type != BACKEND_NAME:
+            return original(self, backend_name, backend_map, error_template)
+        from .backend import B200AttnBackend, B200MultiStepDraftBackend
+
+        is_decode_map = getattr(backend_map.get("triton"), "__name__", "").endswith("_decode_backend")
+        if not is_decode_map:
+            return B200AttnBackend(self.draft_model_runner, skip_prefill=False)
+        if int(self.topk) == 1:
+            return B200MultiStepDraftBackend(self.draft_model_runner, self.topk, self.speculative_num_steps)
+        return backend_map["triton"]()
+
+    DraftBackendFactory._create_backend = _create_backend
+    DraftBackendFactory._b200_patched = True
