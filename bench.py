@@ -389,6 +389,18 @@ def secondary_measurements():
                     "frac_of_8TBs": r["frac_8tbs"]}
         r = sweep.store_case("cfg5 KV store 131072 rows bf16", 131072, 8, 128, bf, 10)
         out["cfg5_kv_store"] = {"GBps": r["gbs"], "us": r["us"], "frac_of_measured_hbm": r["frac_measured"]}
+        # outside BASELINE's configs, same ops API: speculative verify (tree mask over 8 draft tokens) with the
+        # backend's split-KV choice, and the head dims / pool dtypes that left the CUDA-core kernels this round
+        for bs, ctx in ((1, 32768), (8, 16384), (64, 4096)):
+            r0 = sweep.extend_case("verify unsplit", bs, ctx, 8, 32, 8, 128, 5, shared=False, tree_mask=True,
+                                   one_tile=True, splits=1)
+            r1 = sweep.extend_case("verify split", bs, ctx, 8, 32, 8, 128, 5, shared=False, tree_mask=True,
+                                   one_tile=True, splits=0)
+            out[f"verify_bs{bs}_ctx{ctx}"] = {"ms": r1["ms"], "ms_unsplit": r0["ms"], "splits": r1["splits"]}
+        r = sweep.decode_case("gpt-oss heads 64/8 D 64, fp8-e4m3 KV, bs 64 @ 8192", 64, 8192, 64, 8, 64, e4, 1, 10)
+        out["d64_fp8_decode"] = {"GBps": r["gbs"], "us": r["us"], "frac_of_8TBs": r["frac_8tbs"]}
+        r = sweep.decode_case("phi-3-mini heads 32/32 D 96, bs 64 @ 8192", 64, 8192, 32, 32, 96, bf, 1, 10)
+        out["d96_decode"] = {"GBps": r["gbs"], "us": r["us"], "frac_of_8TBs": r["frac_8tbs"]}
     except Exception as e:  # side measurements must never take the headline line down
         out["error"] = f"{type(e).__name__}: {e}"
     return out
