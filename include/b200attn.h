@@ -22,6 +22,8 @@
  *                            split-KV stage 1 + stage-2 merge)
  *   b200attn_decode_static_ws  none: no counterpart in the reference, added
  *                            (b200attn_decode with the split workspace in a static device array; see below)
+ *   b200attn_draft_table     kernels/ops/speculative/cache_locs.py:56-130 (generate_draft_decode_kv_indices: the kv
+ *                            positions branch t of a tree draft attends at step i), triton_backend.py:1912-1955
  *   b200attn_extend_plan     srt/layers/attention/triton_backend.py:860-900 (qo_indptr / kv_indptr for extend)
  *   b200attn_rope_store_kv   srt/layers/rotary_embedding/base.py:234-275,363-385 + set_kv_buffer (see below)
  *   b200attn_extend          srt/layers/attention/torch_native_backend.py:61-174 (oracle semantics),
@@ -38,7 +40,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 6
+#define B200ATTN_ABI_VERSION 7
 
 typedef void* b200_stream_t; /* a cudaStream_t */
 
@@ -198,6 +200,31 @@ int b200attn_decode(const b200_decode_args* args, b200_stream_t stream);
  * ------------------------------------------------------------------------ */
 #define B200_DECODE_STATIC_WS_BYTES (16 * 1024 * 1024)
 int b200attn_decode_static_ws(const b200_decode_args* args, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------ *
+ * EAGLE tree drafting (topk > 1): branch t of request b attends the request's prefix plus the tokens drafted on ITS
+ * branch, whose slots the worker keeps at req_to_token[b, seq_len + t * num_steps + j] (page_size 1 or topk 1) or at the
+ * page-aligned position of generate_draft_decode_kv_indices (cache_locs.py:104-122) -- not a prefix of the row.  This
+ * builds, once per draft, one page-table row per (request, branch):
+ *   table[b * topk + t, 0 .. seq_len)            = req_to_token[pool(b), 0 .. seq_len)
+ *   table[b * topk + t, seq_len + j], j < num_steps = the branch's j-th drafted slot
+ * so that step i of the draft is a plain b200attn_decode over `table` with lengths seq_len + i + 1 and
+ * req_pool_indices = 0 .. num_seqs * topk - 1.  Copies only seq_len + num_steps entries per row (read on the device):
+ * static launch shape, CUDA-graph recordable.
+ * ------------------------------------------------------------------------ */
+typedef struct b200_draft_table_args {
+  const int32_t* req_to_token;
+  int64_t req_to_token_stride;   /* also the readable width of a row */
+  const void* req_pool_indices;  /* [num_seqs] */
+  int32_t req_pool_indices_is_i64;
+  const void* seq_lens;          /* [num_seqs] prefix lengths */
+  int32_t seq_lens_is_i64;
+  int32_t num_seqs, topk, num_steps, page_size;
+  int32_t* table;                /* [num_seqs * topk, table_stride] */
+  int64_t table_stride;
+} b200_draft_table_args;
+
+int b200attn_draft_table(const b200_draft_table_args* args, b200_stream_t stream);
 
 /* 1 if the fast (mma) decode kernel covers this shape, else 0 */
 int b200attn_decode_fast_supported(int32_t head_dim_qk, int32_t head_dim_v, int32_t group,

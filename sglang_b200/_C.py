@@ -14,7 +14,7 @@ LIB_PATH = Path(os.environ.get("B200ATTN_LIB", _PKG_DIR / "lib" / "libb200attn.s
 
 B200_BF16, B200_F16, B200_FP8_E4M3, B200_FP8_E5M2 = 0, 1, 2, 3
 KERNEL_AUTO, KERNEL_GENERIC, KERNEL_FAST = 0, 1, 2
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 i32, i64, f32, vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
@@ -50,6 +50,16 @@ class DecodePlanArgs(C.Structure):
         ("seq_lens", vp), ("seq_lens_is_i64", i32), ("batch_size", i32), ("max_bs", i32),
         ("max_chunks", i32), ("num_kv_heads", i32), ("num_ctas", i32), ("waves", i32),
         ("min_chunk_tokens", i32), ("fixed_chunk_tokens", i32), ("plan", vp), ("window_keys", i32),
+    ]
+
+
+class DraftTableArgs(C.Structure):
+    _fields_ = [
+        ("req_to_token", vp), ("req_to_token_stride", i64),
+        ("req_pool_indices", vp), ("req_pool_indices_is_i64", i32),
+        ("seq_lens", vp), ("seq_lens_is_i64", i32),
+        ("num_seqs", i32), ("topk", i32), ("num_steps", i32), ("page_size", i32),
+        ("table", vp), ("table_stride", i64),
     ]
 
 
@@ -132,6 +142,7 @@ SYMBOLS = {
     "b200attn_device_info": (C.c_int, [C.POINTER(C.c_int)] * 3),
     "b200attn_store_kv": (C.c_int, [C.POINTER(StoreKVArgs), vp]),
     "b200attn_decode_plan_ints": (i64, [i32, i32]),
+    "b200attn_draft_table": (C.c_int, [C.POINTER(DraftTableArgs), vp]),
     "b200attn_rope_store_kv": (C.c_int, [C.POINTER(RopeStoreArgs), vp]),
     "b200attn_decode_plan": (C.c_int, [C.POINTER(DecodePlanArgs), vp]),
     "b200attn_decode": (C.c_int, [C.POINTER(DecodeArgs), vp]),

@@ -160,6 +160,7 @@ class B200AttnBackend(_Base):
         # > 0: this instance is step (offset - 1) of a multi-step draft decode (see B200MultiStepDraftBackend)
         self.draft_step_offset = 0
         self._draft_seq_lens = {}
+        self._draft_tree = None                               # tree drafting: the wrapper's per-branch page table
         self._ext_short = False                               # the host knows that no request extends by more than one tile
         self.num_draft_tokens = _spec_num_draft_tokens(model_runner)
         self.forward_metadata = None
@@ -249,7 +250,8 @@ class B200AttnBackend(_Base):
         if in_capture:
             self._graph_state_frozen = True
         if mode.is_decode_or_idle():
-            if forward_batch.batch_size > self.decode_ws.max_bs:
+            rows = forward_batch.batch_size * (self._draft_tree.topk if self._draft_tree is not None else 1)
+            if rows > self.decode_ws.max_bs:
                 raise ValueError(f"batch size {forward_batch.batch_size} exceeds the decode workspace "
                                  f"({self.decode_ws.max_bs} requests)")
             return
@@ -334,7 +336,8 @@ class B200AttnBackend(_Base):
         if mode.is_idle():
             return
         if mode.is_decode():
-            seq_lens = self._decode_seq_lens(forward_batch, forward_batch.batch_size, refresh=True)
+            rows = forward_batch.batch_size * (self._draft_tree.topk if self._draft_tree is not None else 1)
+            _, _, seq_lens = self._decode_inputs(forward_batch, rows, refresh=True)
             ops.decode_plan(self.decode_ws, seq_lens, self.num_kv_head, waves=self.DECODE_WAVES,
                             items_per_chunk=self._decode_items)
             if self.decode_ws_swa is not None:
@@ -350,6 +353,15 @@ class B200AttnBackend(_Base):
                             req_to_token=self.req_to_token_pool.req_to_token if paged else None,
                             req_pool_indices=forward_batch.req_pool_indices[: ext.shape[0]] if paged else None,
                             extend_prefix_lens=pre if paged else None)
+
+    def _decode_inputs(self, forward_batch, rows: int, refresh: bool = False):
+        """(page table, request rows, lengths) of a decode launch over `rows` query rows.  Tree drafting
+        (B200MultiStepDraftBackend with topk > 1) substitutes the per-branch table its wrapper builds once per draft."""
+        tree = self._draft_tree
+        if tree is not None:
+            return tree.table, tree.rpi[:rows], tree.seq[self.draft_step_offset - 1][:rows]
+        return (self.req_to_token_pool.req_to_token, forward_batch.req_pool_indices[:rows],
+                self._decode_seq_lens(forward_batch, rows, refresh))
 
     def _decode_seq_lens(self, forward_batch, bs: int, refresh: bool = False):
         """The lengths a decode step attends.  A plain backend reads `forward_batch.seq_lens`.  Step i of a multi-step
@@ -490,12 +502,12 @@ class B200AttnBackend(_Base):
         k_descale, v_descale = self._descale(layer)
         bs = q.shape[0]
         window_keys = self._window_keys(layer)
+        rtt, rpi, seq_lens = self._decode_inputs(forward_batch, bs)
         ops.decode_attention(
             q.view(bs, layer.tp_q_head_num, layer.qk_head_dim),
             o.view(bs, layer.tp_q_head_num, layer.v_head_dim),
             k_buf, v_buf,
-            self.req_to_token_pool.req_to_token,
-            forward_batch.req_pool_indices[:bs], self._decode_seq_lens(forward_batch, bs),
+            rtt, rpi, seq_lens,
             self.decode_ws_swa if window_keys else self.decode_ws, layer.scaling,
             kv_dtype=self.kv_dtype, k_scale=k_descale, v_scale=v_descale,
             logit_cap=self._logit_cap(layer), kernel=self.decode_kernel,
@@ -554,6 +566,36 @@ class B200AttnBackend(_Base):
         return True
 
 
+class _DraftTree:
+    """Per-branch page table of an EAGLE tree draft (topk > 1) and the per-step lengths: built once per draft by
+    `refresh` (graph-recordable), shared by the per-step backends."""
+
+    def __init__(self, topk: int, num_steps: int, page_size: int, device):
+        self.topk, self.num_steps, self.page_size, self.device = int(topk), int(num_steps), int(page_size), device
+        self.table = self.rpi = self.seq = None
+        self.frozen = False
+
+    def ensure(self, rows: int, width: int):
+        if self.table is not None and self.table.shape[0] >= rows and self.table.shape[1] >= width:
+            return
+        if self.frozen:
+            raise RuntimeError("b200 backend: the draft table would have to grow after a CUDA-graph capture")
+        self.table = torch.zeros(rows, width, dtype=torch.int32, device=self.device)
+        self.rpi = torch.arange(rows, dtype=torch.int64, device=self.device)
+        self.seq = torch.ones(max(self.num_steps - 1, 1), rows, dtype=torch.int32, device=self.device)
+
+    def refresh(self, forward_batch, req_to_token):
+        bs = int(forward_batch.batch_size)
+        rows = bs * self.topk
+        self.ensure(rows, req_to_token.shape[1])
+        seq = forward_batch.seq_lens[:bs]
+        ops.build_draft_table(self.table, req_to_token, forward_batch.req_pool_indices[:bs], seq, self.topk,
+                              self.num_steps, self.page_size)
+        base = seq.to(torch.int32).repeat_interleave(self.topk)
+        for i in range(self.num_steps - 1):
+            torch.add(base, i + 1, out=self.seq[i][:rows])
+
+
 class B200MultiStepDraftBackend:
     """EAGLE draft decode over several consecutive steps with `--speculative-eagle-topk 1` (chain drafting): the
     reference wraps `speculative_num_steps - 1` per-step backends in one object that the draft worker initialises once
@@ -561,23 +603,34 @@ class B200MultiStepDraftBackend:
     eagle_worker_v2.py:608-650 runs step i under `attn_backends[i]`).  The Triton version materialises per-step
     kv_indices (`generate_draft_decode_kv_indices`); for topk 1 those are the request's `req_to_token` row up to
     `seq_len + i + 1`, which this backend's decode kernels read directly -- so a step is a plain decode whose lengths
-    are `seq_lens + i + 1`.  Tree drafting (topk > 1) attends a non-contiguous slice of the row per branch and keeps
-    the Triton wrapper (sglang_b200.plugin)."""
+    are `seq_lens + i + 1`.  Tree drafting (topk > 1): branch t attends the prefix plus the slots drafted on its own
+    branch, a non-contiguous slice of the row -- `_DraftTree` builds one page-table row per (request, branch) once per
+    draft (`b200attn_draft_table`, the dynamic-length counterpart of the reference's per-step kv_indices copy), and the
+    steps are plain decodes over that table with num_seqs x topk rows."""
 
     needs_cpu_seq_lens: bool = False
 
     def __init__(self, model_runner, topk: int, speculative_num_steps: int):
-        if int(topk) != 1:
-            raise ValueError("B200MultiStepDraftBackend covers chain drafting (topk 1) only")
-        self.topk = 1
+        self.topk = int(topk)
+        if self.topk < 1:
+            raise ValueError("B200MultiStepDraftBackend: topk must be >= 1")
         self.speculative_num_steps = int(speculative_num_steps)
+        self.device = model_runner.device
         self.attn_backends = []
+        page_size = int(getattr(model_runner, "page_size", 1) or 1)
+        # chain drafting reads the request's own req_to_token row; tree drafting needs one row per branch
+        self._tree = _DraftTree(self.topk, self.speculative_num_steps, page_size, self.device) if self.topk > 1 else None
         for i in range(self.speculative_num_steps - 1):
             b = B200AttnBackend(model_runner, skip_prefill=True)
             b.draft_step_offset = i + 1
+            if self._tree is not None:                      # a launch has num_seqs x topk query rows
+                b._draft_tree = self._tree
+                b.max_bs = b.max_bs * self.topk
+                b.decode_ws = ops.DecodeWorkspace.create(b.max_bs, b.num_head, b.v_head_dim, b.device,
+                                                         num_ctas=b.decode_ctas, waves=b.DECODE_WAVES)
+                b.decode_ws_swa = b._swa_workspace(b.decode_ws)
             self.attn_backends.append(b)
         self.max_context_len = self.attn_backends[0].max_context_len if self.attn_backends else None
-        self.device = model_runner.device
         self.req_to_token_pool = model_runner.req_to_token_pool
         self.token_to_kv_pool = model_runner.token_to_kv_pool
 
@@ -605,14 +658,21 @@ class B200MultiStepDraftBackend:
             out_cache_loc=getattr(forward_batch, "out_cache_loc", None),
             positions=getattr(forward_batch, "positions", None), spec_info=getattr(forward_batch, "spec_info", None))
 
+    def _refresh_tree(self, forward_batch):
+        if self._tree is not None and self.attn_backends:
+            self._tree.refresh(forward_batch, self.req_to_token_pool.req_to_token)
+
     def init_forward_metadata(self, forward_batch):
         view = self._decode_view(forward_batch)
+        self._refresh_tree(view)
         for b in self.attn_backends:
             b.init_forward_metadata(view)
 
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
+        if self._tree is not None:
+            self._tree.ensure(int(max_bs) * self.topk, self.req_to_token_pool.req_to_token.shape[1])
         for b in self.attn_backends:
-            b.init_cuda_graph_state(max_bs, max_num_tokens)
+            b.init_cuda_graph_state(int(max_bs) * self.topk, max_num_tokens)
             n = max(int(max_bs), b.max_bs)
             for dt in (torch.int32, torch.int64):       # the per-step length buffers a captured graph will hold
                 if dt not in b._draft_seq_lens or b._draft_seq_lens[dt].numel() < n:
@@ -620,11 +680,15 @@ class B200MultiStepDraftBackend:
 
     def init_forward_metadata_out_graph(self, forward_batch, in_capture: bool = False):
         view = self._decode_view(forward_batch)
+        if self._tree is not None:
+            self._tree.ensure(int(view.batch_size) * self.topk, self.req_to_token_pool.req_to_token.shape[1])
+            self._tree.frozen = self._tree.frozen or in_capture
         for b in self.attn_backends:
             b.init_forward_metadata_out_graph(view, in_capture=in_capture)
 
     def init_forward_metadata_in_graph(self, forward_batch):
         view = self._decode_view(forward_batch)
+        self._refresh_tree(view)
         for b in self.attn_backends:
             b.init_forward_metadata_in_graph(view)
 

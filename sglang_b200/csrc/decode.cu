@@ -412,6 +412,48 @@ extern "C" int b200attn_decode_plan(const b200_decode_plan_args* a, b200_stream_
   return B200_OK;
 }
 
+namespace b200 {
+namespace {
+constexpr int kDraftTableThreads = 256;
+
+__global__ void __launch_bounds__(kDraftTableThreads) draft_table_kernel(const b200_draft_table_args a) {
+  const int row = blockIdx.x;
+  const int b = row / a.topk, t = row - b * a.topk;
+  const int64_t L64 = load_index(a.seq_lens, a.seq_lens_is_i64, b);
+  const int64_t width = a.req_to_token_stride < a.table_stride ? a.req_to_token_stride : a.table_stride;
+  const int L = (int)(L64 < 0 ? 0 : (L64 < width ? L64 : width));
+  const int32_t* src = a.req_to_token + load_index(a.req_pool_indices, a.req_pool_indices_is_i64, b) * a.req_to_token_stride;
+  int32_t* dst = a.table + (int64_t)row * a.table_stride;
+  for (int p = threadIdx.x; p < L; p += kDraftTableThreads) dst[p] = __ldg(src + p);
+  // first drafted slot of this branch inside the request's row (cache_locs.py:104-122)
+  int64_t start;
+  if (a.page_size == 1 || a.topk == 1) {
+    start = (int64_t)L + (int64_t)t * a.num_steps;
+  } else {
+    const int last_page_len = L % a.page_size;
+    const int new_pages = (last_page_len + a.num_steps + a.page_size - 1) / a.page_size;
+    start = (int64_t)(L / a.page_size) * a.page_size + (int64_t)t * new_pages * a.page_size + last_page_len;
+  }
+  for (int j = threadIdx.x; j < a.num_steps; j += kDraftTableThreads)
+    if (L + j < a.table_stride) dst[L + j] = start + j < a.req_to_token_stride ? __ldg(src + start + j) : 0;
+}
+}  // namespace
+}  // namespace b200
+
+extern "C" int b200attn_draft_table(const b200_draft_table_args* a, b200_stream_t stream_) {
+  using namespace b200;
+  B200_CHECK_ARG(a != nullptr, "draft_table: null args");
+  if (a->num_seqs == 0) return B200_OK;
+  B200_CHECK_ARG(a->req_to_token && a->req_pool_indices && a->seq_lens && a->table, "draft_table: null pointer");
+  B200_CHECK_ARG(a->num_seqs > 0 && a->topk > 0 && a->num_steps > 0 && a->page_size > 0 && a->table_stride > 0 &&
+                     a->req_to_token_stride > 0,
+                 "draft_table: num_seqs %d topk %d num_steps %d page_size %d", a->num_seqs, a->topk, a->num_steps,
+                 a->page_size);
+  draft_table_kernel<<<(unsigned)(a->num_seqs * a->topk), kDraftTableThreads, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(*a);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
 extern "C" int b200attn_decode_fast_supported(int32_t dqk, int32_t dv, int32_t group, int32_t q_dtype,
                                               int32_t kv_dtype) {
   return b200::decode_fast_supported(dqk, dv, group, q_dtype, kv_dtype) ? 1 : 0;

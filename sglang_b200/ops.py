@@ -327,6 +327,32 @@ def decode_attention(
     return o
 
 
+def build_draft_table(table: torch.Tensor, req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
+                      seq_lens: torch.Tensor, topk: int, num_steps: int, page_size: int = 1) -> torch.Tensor:
+    """EAGLE tree drafting: fill `table` [num_seqs * topk, W] (int32) with one page-table row per (request, branch):
+    the request's prefix followed by that branch's drafted slots (reference
+    kernels/ops/speculative/cache_locs.py:56-130), so that step i of the draft is a plain decode over `table` with
+    lengths `seq_lens + i + 1`.  Graph-recordable (lengths are read on the device)."""
+    global launch_count
+    _need_cuda(table, req_to_token, req_pool_indices, seq_lens)
+    n = seq_lens.shape[0]
+    if table.dtype != torch.int32 or table.dim() != 2 or table.stride(1) != 1 or table.shape[0] < n * topk:
+        raise ValueError("table must be int32 [>= num_seqs * topk, W] with contiguous rows")
+    if req_to_token.dtype != torch.int32 or req_to_token.stride(1) != 1:
+        raise ValueError("req_to_token must be int32 with contiguous rows")
+    a = _C.DraftTableArgs(
+        req_to_token=req_to_token.data_ptr(), req_to_token_stride=req_to_token.stride(0),
+        req_pool_indices=req_pool_indices.data_ptr(),
+        req_pool_indices_is_i64=_index_kind(req_pool_indices, "req_pool_indices"),
+        seq_lens=seq_lens.data_ptr(), seq_lens_is_i64=_index_kind(seq_lens, "seq_lens"),
+        num_seqs=n, topk=int(topk), num_steps=int(num_steps), page_size=max(1, int(page_size)),
+        table=table.data_ptr(), table_stride=table.stride(0),
+    )
+    _C.check(_C.lib.b200attn_draft_table(C.byref(a), _stream()), "draft_table")
+    launch_count += 1
+    return table
+
+
 def decode_fast_supported(head_dim_qk: int, head_dim_v: int, group: int, q_dtype, kv_dtype) -> bool:
     return bool(_C.lib.b200attn_decode_fast_supported(head_dim_qk, head_dim_v, group, dtype_code(q_dtype),
                                                       dtype_code(kv_dtype)))

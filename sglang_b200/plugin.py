@@ -43,8 +43,7 @@ def _patch_draft_backend_factory() -> None:
     """Speculative decoding: `DraftBackendFactory` resolves the draft model's backends through dicts that are local to
     its methods (speculative/draft_utils.py:60-135), so a plugin backend name ends in "EAGLE is not supported in
     attention backend b200".  Teach `_create_backend` the name: the draft-extend backend is a `B200AttnBackend`, the
-    multi-step draft-decode backend is `B200MultiStepDraftBackend` for chain drafting (topk 1) and the reference's own
-    Triton wrapper for tree drafting (its per-branch kv indices are not a prefix of the `req_to_token` row)."""
+    multi-step draft-decode backend is `B200MultiStepDraftBackend` (chain and tree drafting)."""
     try:
         from sglang.srt.speculative.draft_utils import DraftBackendFactory  # type: ignore
     except Exception:
@@ -64,9 +63,7 @@ def _patch_draft_backend_factory() -> None:
         is_decode_map = getattr(backend_map.get("triton"), "__name__", "").endswith("_decode_backend")
         if not is_decode_map:
             return B200AttnBackend(self.draft_model_runner, skip_prefill=False)
-        if int(self.topk) == 1:
-            return B200MultiStepDraftBackend(self.draft_model_runner, self.topk, self.speculative_num_steps)
-        return backend_map["triton"]()
+        return B200MultiStepDraftBackend(self.draft_model_runner, self.topk, self.speculative_num_steps)
 
     DraftBackendFactory._create_backend = _create_backend
     DraftBackendFactory._b200_patched = True
