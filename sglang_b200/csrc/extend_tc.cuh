@@ -248,10 +248,14 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
   const bool use_tma = kTma && p.plan[kPlanPageRows] == p.tma_rows;
 
   // ---- one-time setup --------------------------------------------------------------------------
+  // D = 256 with FP8 pools is producer-bound (two widened fills per 1 280 MMA cycles): the one-tile layout's idle
+  // warps 4-7 (the second tile's softmax warpgroup) fill and widen as well -- 8 producer warps, 8 kv rows each
+  constexpr bool kWideProd = kFp8 && kHD == 256;
+  constexpr int kProdThreadsAll = kWideProd ? 2 * kProducerThreads : kProducerThreads;
   if (threadIdx.x == 0) {
-    mbar_init(bar(kBarQFull), kProducerThreads);
+    mbar_init(bar(kBarQFull), kProdThreadsAll);
     for (int s = 0; s < kSlots; ++s) {
-      mbar_init(bar(kBarFull + s), use_tma ? 1 : kProducerThreads);
+      mbar_init(bar(kBarFull + s), use_tma ? 1 : kProdThreadsAll);
       mbar_init(bar(kBarEmpty + s), 1);
     }
     for (int t = 0; t < kQTiles; ++t) {                   // (one-tile instance: S buffer t; ODone + 1 = "PV done")
@@ -268,7 +272,7 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
-  if (warp >= kProducerWarp0) {
+  if (warp >= kProducerWarp0 || (kWideProd && warp >= kSoftmaxWarps && warp < 2 * kSoftmaxWarps)) {
     setmaxnreg_dec<kRegsOther>();
     if constexpr (kFp8) {
 #include "extend_tc_producer_fp8.inc"
