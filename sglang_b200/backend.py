@@ -123,8 +123,10 @@ class B200AttnBackend(_Base):
         sw = getattr(model_runner, "sliding_window_size", None)
         self.sliding_window_size = int(sw) if sw is not None and sw > -1 else None
         if hasattr(pool, "translate_loc_from_full_to_swa"):
-            raise NotImplementedError("b200 backend: the separate SWA KV pool (SWAKVPool) is not supported; "
-                                      "sliding-window layers read the full pool")
+            raise NotImplementedError(
+                "b200 backend: the separate SWA KV pool (SWAKVPool) is not supported -- launch hybrid sliding-window "
+                "models with --disable-hybrid-swa-memory so that every layer uses the full MHATokenToKVPool "
+                "(sliding-window layers then read their window from it)")
 
         self.max_bs = int(self.req_to_token_pool.size)
         self.max_context_len = int(getattr(cfg, "context_len", self.req_to_token_pool.max_context_len))
