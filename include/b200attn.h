@@ -226,7 +226,9 @@ typedef struct b200_draft_table_args {
 
 int b200attn_draft_table(const b200_draft_table_args* args, b200_stream_t stream);
 
-/* 1 if the fast (mma) decode kernel covers this shape, else 0 */
+/* 1 if the per-head tensor-core decode kernel covers this shape, else 0.  The head-group kernel (4 adjacent kv heads
+ * per CTA, picked when num_kv_heads % 4 == 0) additionally covers D = 64 with FP8 pools and D = 80 / 96 / 112 with
+ * 16-bit pools; b200attn_decode_items_per_chunk() returns num_kv_heads / 4 exactly when it will run. */
 int b200attn_decode_fast_supported(int32_t head_dim_qk, int32_t head_dim_v, int32_t group,
                                    int32_t q_dtype, int32_t kv_dtype);
 /* persistent CTAs per SM the fast decode kernel is tuned for */
