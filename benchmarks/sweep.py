@@ -140,10 +140,12 @@ def extend_case(name, bs, P, E, Hq, Hkv, D, iters, shared=True, kernel=0, pool_d
         mkw = dict(custom_mask=m.reshape(-1), mask_skip_prefix=True,
                    mask_indptr=torch.arange(bs + 1, device=dev, dtype=torch.int64) * (E * (P + E)))
 
-    if splits == 0:
-        splits = ops.extend_pick_splits(bs * Hkv, sm)
+    hint = 0
+    if splits == 0:       # the backend's choice: one tile per request, exact count handed over (tail-only above one wave)
+        splits, hint = ops.extend_pick_splits(bs * Hkv, sm), bs
     if splits > 1:
-        mkw.update(num_splits=splits, split_ws=torch.empty(ops.extend_split_ws_floats(splits, T, Hq, D), device=dev))
+        mkw.update(num_splits=splits, split_ws=torch.empty(ops.extend_split_ws_floats(splits, T, Hq, D), device=dev),
+                   num_tiles_hint=hint)
 
     def fn():
         ops.extend_attention(q, o, kp, vp, rtt, rpi, pre, ext, ws, D**-0.5, kernel=kernel, kv_dtype=pool_dtype,
@@ -238,7 +240,8 @@ def main():
         # speculative verify (tree mask over 8 draft tokens) and short extends at several batch sizes: unsplit
         # one-tile items against the split-KV the backend picks from bs x Hkv
         it = max(5, a.iters // 3)
-        for bs, P in ((64, 4096), (16, 4096), (4, 4096), (1, 4096), (1, 32768), (8, 16384), (64, 512)):
+        for bs, P in ((64, 4096), (40, 4096), (24, 4096), (16, 4096), (4, 4096), (1, 4096), (1, 32768), (8, 16384),
+                      (64, 512)):
             for sp in (1, 0):
                 emit(extend_case(f"verify {bs} req x ({P} + 8 draft, tree mask), one-tile, splits {'auto' if sp == 0 else sp}",
                                  bs, P, 8, 32, 8, 128, it, shared=False, tree_mask=True, one_tile=True, splits=sp))

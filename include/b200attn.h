@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 7
+#define B200ATTN_ABI_VERSION 8
 
 typedef void* b200_stream_t; /* a cudaStream_t */
 
@@ -328,6 +328,11 @@ typedef struct b200_extend_args {
   int32_t num_splits;
   float* split_ws;              /* >= b200attn_extend_split_ws_floats(...) floats; required when num_splits > 1 */
   int64_t split_ws_floats;      /* capacity of split_ws */
+  int32_t num_tiles_hint;       /* exact number of plan tiles when the host knows it (speculative batches: one per
+                                   request), 0 = unknown.  With it, a batch of MORE work items than SMs is split in
+                                   the tail only: the tiles that fill whole waves run unsplit, the remaining ones are
+                                   cut into min(num_splits, SMs / tail items) parts so that the last, partly filled
+                                   wave ends earlier (two attention launches + the merge) */
 } b200_extend_args;
 
 int b200attn_extend(const b200_extend_args* args, b200_stream_t stream);

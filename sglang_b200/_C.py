@@ -14,7 +14,7 @@ LIB_PATH = Path(os.environ.get("B200ATTN_LIB", _PKG_DIR / "lib" / "libb200attn.s
 
 B200_BF16, B200_F16, B200_FP8_E4M3, B200_FP8_E5M2 = 0, 1, 2, 3
 KERNEL_AUTO, KERNEL_GENERIC, KERNEL_FAST = 0, 1, 2
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 i32, i64, f32, vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
@@ -108,7 +108,7 @@ class ExtendArgs(C.Structure):
         ("num_ctas", i32), ("kernel", i32), ("lse", vp), ("pool_slots", i64),
         ("window_keys", i32), ("sinks", vp), ("custom_mask", vp), ("mask_indptr", vp), ("mask_skip_prefix", i32),
         ("block_q", i32), ("page_size", i32),
-        ("num_splits", i32), ("split_ws", vp), ("split_ws_floats", i64),
+        ("num_splits", i32), ("split_ws", vp), ("split_ws_floats", i64), ("num_tiles_hint", i32),
     ]
 
 

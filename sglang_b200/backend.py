@@ -159,6 +159,7 @@ class B200AttnBackend(_Base):
                                                              self.kv_dtype, self.extend_kernel)
         self._ext_block_q = self._extend_block_q      # block_q of the current forward's plan
         self._ext_splits, self._ext_split_ws = 1, None      # split-KV choice of the current forward (one-tile plans)
+        self._ext_tiles = 0                                   # ... and the exact tile count handed to the library
         # > 0: this instance is step (offset - 1) of a multi-step draft decode (see B200MultiStepDraftBackend)
         self.draft_step_offset = 0
         self._draft_seq_lens = {}
@@ -307,7 +308,8 @@ class B200AttnBackend(_Base):
             self._ext_block_q = self._pick_block_q(max(lens_cpu) if lens_cpu is not None and len(lens_cpu) else None)
             self._ext = self._select_ext((int(mode), bs), bs, int(T), 0, in_capture)
             self._ext_lens = (forward_batch.extend_prefix_lens, forward_batch.extend_seq_lens, None, None)
-            self._plan_splits(bs, int(T), self._kv_hint(forward_batch, bs, in_capture))
+            n_ext = sum(1 for e in lens_cpu if int(e) > 0) if lens_cpu is not None and len(lens_cpu) == bs else 0
+            self._plan_splits(bs, int(T), self._kv_hint(forward_batch, bs, in_capture), tiles=n_ext)
 
     @staticmethod
     def _kv_hint(forward_batch, bs: int, in_capture: bool) -> int:
@@ -318,17 +320,18 @@ class B200AttnBackend(_Base):
             return 0
         return total // bs
 
-    def _plan_splits(self, bs: int, tokens: int, kv_hint: int = 0):
+    def _plan_splits(self, bs: int, tokens: int, kv_hint: int = 0, tiles: int = 0):
         """Split-KV for one-tile plans (speculative verify / draft extend / a few new tokens): bs x Hkv work items
         rarely fill the SMs, so every item's kv range is cut into parts (ops.extend_pick_splits; the device trims the
         count for short contexts).  Under capture it is chosen from the batch shape alone (a graph keeps its choice);
         eager batches add the mean context length (`seq_lens_sum`, a host int) as a hint."""
-        self._ext_splits, self._ext_split_ws = 1, None
+        self._ext_splits, self._ext_split_ws, self._ext_tiles = 1, None, 0
         if not self._ext_short or bs <= 0 or tokens <= 0:       # (D = 256 plans are always one-tile: long prefills stay unsplit)
             return
-        s = ops.extend_pick_splits(bs * self.num_kv_head, self.sm_count, kv_hint)
+        tiles = int(tiles) if tiles > 0 else bs          # short plans: one tile per request that extends at all
+        s = ops.extend_pick_splits(tiles * self.num_kv_head, self.sm_count, kv_hint)
         if s > 1:
-            self._ext_splits = s
+            self._ext_splits, self._ext_tiles = s, tiles
             self._ext_split_ws = self._ext.split_buffer(
                 ops.extend_split_ws_floats(s, tokens, self.num_head, self.v_head_dim))
 
@@ -558,7 +561,7 @@ class B200AttnBackend(_Base):
             kernel=self.extend_kernel, lse=lse,
             window_keys=self._window_keys(layer) if causal else 0, sinks=self._sinks(kwargs, q.device),
             custom_mask=custom_mask, mask_indptr=mask_indptr, mask_skip_prefix=True, page_size=self.page_size,
-            num_splits=self._ext_splits, split_ws=self._ext_split_ws,
+            num_splits=self._ext_splits, split_ws=self._ext_split_ws, num_tiles_hint=self._ext_tiles,
         )
         if lse is not None:
             return o.view(T, layer.tp_q_head_num, layer.v_head_dim), lse

@@ -11,6 +11,7 @@
 // Algorithmic FLOPs per launch: 4 * Hq * D * sum_r (E_r * P_r + E_r * (E_r + 1) / 2).
 #include <cuda.h>   // CUtensorMap types only; the encoder is resolved through cudaGetDriverEntryPoint
 
+#include <algorithm>
 #include <cstring>
 #include <type_traits>
 
@@ -164,6 +165,9 @@ struct ExtendParams {
   int32_t num_splits;
   float* split_o;
   float* split_lse;
+  // one-tile launches over a sub-range of the plan's tiles (tail-only split): tiles [tile_offset, tile_offset +
+  // tile_count), tile_count 0 = all
+  int32_t tile_offset, tile_count;
   // 16-byte chunks of a real Q/K/V row (head_dim / 8).  Head dims 80 / 96 / 112 run on the D = 128 one-tile instance
   // with the remaining chunks of every tile row zero-filled (exact: the padding multiplies by zero).
   int32_t d_chunks;
@@ -298,7 +302,8 @@ __global__ void __launch_bounds__(kSplitMergeWarps* kWarp) extend_split_merge_ke
   const int h = (int)(idx - tok * Hq);
   const int64_t part = p.num_q_tokens * Hq;                           // rows per split
   const float l = lane < S ? p.split_lse[lane * part + idx] : -INFINITY;
-  if (__shfl_sync(0xffffffffu, l, 0) == INFINITY) return;             // the item was not split: split 0 wrote the row
+  const float l0 = __shfl_sync(0xffffffffu, l, 0);
+  if (l0 == INFINITY || l0 != l0) return;       // not split: split 0 (+inf) or the unsplit launch (NaN fill) wrote the row
   const float m = warp_max(l);
   QT* orow = reinterpret_cast<QT*>(p.o) + tok * p.o_stride_t + (int64_t)h * p.o_stride_h;
   if (m == -INFINITY) {                                               // no part saw a key (cannot happen under the
@@ -357,6 +362,20 @@ extern "C" int64_t b200attn_extend_split_ws_floats(int32_t num_splits, int64_t n
 
 extern "C" int32_t b200attn_extend_pick_splits(int32_t items, int32_t num_sms, int32_t kv_tokens_hint) {
   if (items <= 0 || num_sms <= 0 || items > 8 * num_sms) return 1;    // >= 8 waves: the quantisation loss is small
+  if (items > num_sms) {
+    // several waves: only the tail (the items of the last, partly filled wave) is split, see num_tiles_hint
+    const int tail = items % num_sms, full = items / num_sms;
+    if (tail == 0) return 1;
+    const int S = std::min<int>(B200_EXTEND_MAX_SPLITS, num_sms / tail);
+    if (S < 2) return 1;
+    const double blocks_t = (kv_tokens_hint > 0 ? kv_tokens_hint : 4096) / 128.0 + 1.0;
+    const double pc = 4.0 / blocks_t, mc = 3.7 / blocks_t;
+    // measured on 24 / 40 / 64-request verify batches at 4 K: the second attention launch (it starts when the first
+    // has drained), the NaN fill and the merge cost ~13 kv blocks' worth of time together
+    const double unsplit_t = (full + 1) * (1.0 + pc), tail_t = full * (1.0 + pc) + (1.0 / S + pc) + 13.0 / blocks_t;
+    (void)mc;
+    return tail_t < (kv_tokens_hint > 0 ? 0.95 : 0.90) * unsplit_t ? S : 1;
+  }
   // Makespan in units of one unsplit item: ceil(items * S / SMs) waves, each 1 / S of an item plus the fixed cost of a
   // part (TMEM allocation, Q fill, pipeline ramp, fp32 partial epilogue: ~6.5 us = 4 kv blocks of 1.64 us, measured
   // on the 64 x (4 K + 8) verify shape), plus the merge launch (~6 us) once.  A split has to win by 5 %.
@@ -421,6 +440,7 @@ extern "C" int b200attn_extend(const b200_extend_args* a, b200_stream_t stream_)
   p.custom_mask = a->custom_mask; p.mask_indptr = a->mask_indptr; p.mask_skip_prefix = a->mask_skip_prefix;
   p.kv_e5m2 = a->kv_dtype == B200_FP8_E5M2;
   p.num_splits = 1; p.split_o = nullptr; p.split_lse = nullptr;
+  p.tile_offset = 0; p.tile_count = 0;
   p.d_chunks = a->head_dim_qk / 8;
   p.tma_rows = 0;
   p.pool_slots = a->pool_slots > 0 && a->pool_slots < 0x7fffffff ? (int32_t)a->pool_slots : 0;
@@ -449,6 +469,32 @@ extern "C" int b200attn_extend(const b200_extend_args* a, b200_stream_t stream_)
     p.split_o = a->split_ws;
     // the LSE block starts 16-byte aligned as well: S * T * Hq * Dv floats with Dv a multiple of 64
     p.split_lse = a->split_ws + (int64_t)a->num_splits * a->num_q_tokens * a->num_q_heads * a->head_dim_v;
+    // More work items than SMs and an exact tile count: split the tail only.  The tiles that fill whole waves run
+    // unsplit; the rest (which would occupy a fraction of the SMs for a whole item's time) is cut into parts.
+    if (a->num_tiles_hint > 0) {
+      const int sms = sm_count();
+      const int64_t items = (int64_t)a->num_tiles_hint * a->num_kv_heads;
+      if (items > sms) {
+        const int tiles_full = (int)((items / sms) * sms / a->num_kv_heads);
+        const int tiles_tail = a->num_tiles_hint - tiles_full;
+        const int64_t tail_items = (int64_t)tiles_tail * a->num_kv_heads;
+        const int s_tail = tail_items > 0 ? (int)std::min<int64_t>(a->num_splits, sms / tail_items) : 0;
+        if (tiles_full <= 0 || s_tail < 2) {              // nothing to gain: one unsplit launch
+          p.num_splits = 1;
+          return launch_extend_fast(p, *a, stream);
+        }
+        // rows that no part will write: split 0's LSE = NaN tells the merge to leave them alone
+        B200_CHECK_CUDA(cudaMemsetAsync(p.split_lse, 0xff, (size_t)a->num_q_tokens * a->num_q_heads * sizeof(float), stream));
+        ExtendParams p1 = p;
+        p1.num_splits = 1; p1.tile_offset = 0; p1.tile_count = tiles_full;
+        int rc = launch_extend_fast(p1, *a, stream);
+        if (rc != B200_OK) return rc;
+        p.num_splits = s_tail; p.tile_offset = tiles_full; p.tile_count = tiles_tail;
+        rc = launch_extend_fast(p, *a, stream);
+        if (rc != B200_OK) return rc;
+        return launch_split_merge(p, a->q_dtype, stream);
+      }
+    }
     const int rc = launch_extend_fast(p, *a, stream);
     if (rc != B200_OK) return rc;
     return launch_split_merge(p, a->q_dtype, stream);

@@ -196,8 +196,9 @@ extend_tc_kernel(const ExtendParams p, const int max_tiles, const __grid_constan
   // split-KV (one-tile instances only): blockIdx.x = (item_tile * num_splits + split) * Hkv + kvh
   const int n_splits = kOneTile ? p.num_splits : 1;
   const int item_part = blockIdx.x / Hkv, kvh = blockIdx.x - item_part * Hkv;
-  const int item_tile = kOneTile ? item_part / n_splits : item_part;
-  const int split = kOneTile ? item_part - item_tile * n_splits : 0;
+  const int tile_local = kOneTile ? item_part / n_splits : item_part;       // tile inside this launch's tile range
+  const int split = kOneTile ? item_part - tile_local * n_splits : 0;
+  const int item_tile = kOneTile ? tile_local + p.tile_offset : item_part;
   const int num_tiles = p.plan[0];
   if (item_tile >= num_tiles || item_tile >= max_tiles) return;
   const int32_t* qo_indptr = p.plan + kPlanHeader;
@@ -404,7 +405,8 @@ int launch_extend_fast_t(const ExtendParams& p_in, const b200_extend_args& a, cu
   // host-side bound on the number of work items: sum_r ceil(E_r / block_q) <= T / block_q + bs
   int64_t tiles = a.num_q_tokens / block_q + a.batch_size;
   if (tiles > a.max_tiles) tiles = a.max_tiles;
-  const int64_t grid = tiles * p.num_kv_heads * (kOneTile ? p.num_splits : 1);
+  const int64_t tiles_launch = (kOneTile && p.tile_count > 0) ? p.tile_count : tiles;
+  const int64_t grid = tiles_launch * p.num_kv_heads * (kOneTile ? p.num_splits : 1);
   B200_CHECK_ARG(grid > 0 && grid < 0x7fffffff, "extend: bad grid %lld", (long long)grid);
   B200_CHECK_ARG(kOneTile || p.num_splits == 1, "extend: split-KV needs the one-tile instance");
   kern<<<(unsigned)grid, tc::kThreads, kSmem, stream>>>(p, (int)tiles, tm_k, tm_v);

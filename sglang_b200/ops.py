@@ -468,10 +468,12 @@ def extend_attention(
     page_size: int = 1,
     num_splits: int = 1,
     split_ws: Optional[torch.Tensor] = None,
+    num_tiles_hint: int = 0,
 ) -> torch.Tensor:
     """`num_splits` > 1 (one-tile plans only, see `extend_pick_splits`): split-KV -- every work item's kv range is cut
     into up to `num_splits` parts that run as separate CTAs, `split_ws` (float32, >= `extend_split_ws_floats(...)`)
-    holds their partials and a merge launch follows.
+    holds their partials and a merge launch follows.  `num_tiles_hint`: the exact tile count when the host knows it
+    (one per request for speculative batches) -- batches of more items than SMs are then split in the tail only.
     `page_size`: KV page size of the pool (pages are page_size-aligned runs of consecutive slots).
     `window_keys` > 0: query at position x attends kv positions (x - window_keys, x].  `sinks`: float32 [Hq].
     `custom_mask` (uint8 / bool, flat) + `mask_indptr` (int64 [bs + 1]): request r, query i, kv position x is
@@ -527,6 +529,7 @@ def extend_attention(
         if split_ws.dtype != torch.float32 or not split_ws.is_contiguous():
             raise ValueError("split_ws must be a contiguous float32 tensor")
         a.num_splits, a.split_ws, a.split_ws_floats = int(num_splits), split_ws.data_ptr(), split_ws.numel()
+        a.num_tiles_hint = max(0, int(num_tiles_hint))
     _C.check(_C.lib.b200attn_extend(C.byref(a), _stream()), "extend")
     launch_count += 2 if num_splits > 1 else 1
     return o

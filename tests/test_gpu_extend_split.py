@@ -11,7 +11,8 @@ from test_gpu_extend import make_extend_problem
 pytestmark = pytest.mark.gpu
 
 
-def _run(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, splits, *, page_size=1, want_lse=True, poison=None, **kw):
+def _run(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, splits, *, page_size=1, want_lse=True, poison=None,
+         tiles_hint=0, **kw):
     from sglang_b200 import ops
 
     sm, _, _ = ops.device_info()
@@ -34,7 +35,8 @@ def _run(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, splits, *, page_size=
         if kw.get(name) is not None:
             kw[name] = kw[name].cuda()
     ops.extend_attention(q.cuda(), o, kp.cuda(), vp.cuda(), rtt_g, rpi_g, pre_g, ext_g, ws, scale, kv_dtype=pool_dtype,
-                         lse=lse, page_size=page_size, num_splits=splits, split_ws=split_ws, **kw)
+                         lse=lse, page_size=page_size, num_splits=splits, split_ws=split_ws, num_tiles_hint=tiles_hint,
+                         **kw)
     torch.cuda.synchronize()
     return o.float().cpu(), (lse.cpu() if want_lse else None)
 
@@ -117,6 +119,33 @@ def test_split_kv_extend_tree_mask(skip):
         assert float((lse - want_lse).abs().max()) <= ATOL
 
 
+@pytest.mark.parametrize("bs,pool_dtype", [(24, torch.bfloat16), (40, torch.bfloat16), (21, torch.float8_e4m3fn)])
+def test_split_kv_tail_only_for_batches_above_one_wave(bs, pool_dtype):
+    """More work items than SMs and an exact tile count: the tiles that fill whole waves run unsplit, the tail is cut
+    into parts (two attention launches + merge; rows of the unsplit tiles keep the NaN fill in the split-0 LSE block and
+    are left alone by the merge).  Prefixes include short ones, which the device keeps unsplit inside the tail."""
+    from sglang_b200 import ops
+
+    Hq, Hkv, D, n = 32, 8, 128, 8
+    g = torch.Generator().manual_seed(bs)
+    prefix = torch.randint(200, 2600, (bs,), generator=g).tolist()
+    prefix[-1], prefix[-2] = 300, 2500                   # a short and a long context inside the tail
+    q, kp, vp, rtt, rpi, pre, ext = make_extend_problem(Hq, Hkv, D, prefix, [n] * bs, 1, torch.bfloat16, pool_dtype, seed=bs)
+    sm, _, _ = ops.device_info()
+    splits = max(ops.extend_pick_splits(bs * Hkv, sm), 2)       # (the heuristic may decline; the mechanism is under test)
+    assert bs * Hkv > sm
+    scale = D**-0.5
+    want, want_lse = ref.extend_ref(q, kp, vp, rtt, rpi, pre, ext, scale, kv_dtype=pool_dtype, want_lse=True)
+    got, lse = _run(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, splits, tiles_hint=bs)
+    assert_close_scaled(got, want, f"tail split {splits}")
+    assert float((lse - want_lse).abs().max()) <= ATOL
+    one, lse1 = _run(q, kp, vp, rtt, rpi, pre, ext, scale, pool_dtype, 1)
+    # the tiles of the full waves ran the unsplit kernel: bit-identical rows
+    tiles_full = (bs * Hkv // sm) * sm // Hkv
+    assert torch.equal(got[: tiles_full * n], one[: tiles_full * n])
+    assert float((got - one).abs().max()) <= 2e-2 and float((lse - lse1).abs().max()) <= 2e-3
+
+
 def test_split_kv_short_contexts_are_not_split():
     """The device trims the split count so that a part keeps >= 4 kv blocks: items below 8 blocks are finished by
     split 0 exactly like an unsplit launch (bit-identical), whatever the workspace holds."""
@@ -158,8 +187,11 @@ def test_pick_splits_heuristic():
     assert ops.extend_pick_splits(32, 148) == 4
     assert ops.extend_pick_splits(64, 148) == 2
     assert ops.extend_pick_splits(148, 148) == 1               # exactly one wave
-    assert ops.extend_pick_splits(512, 148) == 1               # 3.46 waves: measured, a split does not pay at 4 K
-    assert ops.extend_pick_splits(512, 148, 65536) > 1         # ... but does behind very long contexts
+    assert ops.extend_pick_splits(512, 148) == 1               # 3.46 waves: cutting 68 tail items in two does not pay
+    assert ops.extend_pick_splits(320, 148) == 6               # 24 tail items behind two full waves (measured -9 %)
+    assert ops.extend_pick_splits(192, 148) == 3               # 44 tail items behind one full wave (measured -11 %)
+    assert ops.extend_pick_splits(600, 148, 8192) == 16        # 8 tail items would otherwise cost a whole wave
+    assert ops.extend_pick_splits(592, 148) == 1               # exactly four waves
     assert ops.extend_pick_splits(64, 148, 256) == 1           # short contexts: fixed costs dominate
     assert ops.extend_pick_splits(4096, 148) == 1              # many waves: nothing to gain
     assert ops.extend_pick_splits(0, 148) == 1
