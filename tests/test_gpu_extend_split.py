@@ -313,3 +313,39 @@ def test_extend_d80_d96_d112_on_the_padded_d128_tile(shape, dtype):
     want_o = ref.extend_ref(q, kp, vp, rtt, rpi, pre, ext, scale, kv_dtype=dtype, **kw)
     got_o, _ = _run(q, kp, vp, rtt, rpi, pre, ext, scale, dtype, 1, page_size=page, **dict(kw))
     assert_close_scaled(got_o, want_o, "window + cap + sinks")
+
+
+def test_backend_verify_tail_split_above_one_wave():
+    """TARGET_VERIFY through the plugin API with more work items than SMs (24 requests x 8 kv heads): the backend hands
+    the exact tile count over and the library splits the tail only."""
+    from types import SimpleNamespace
+
+    from sglang_b200.srt_mirror import ForwardBatch, ForwardMode, RadixAttention
+    from test_gpu_features import _backend_problem
+
+    Hq, Hkv, D, n, bs = 32, 8, 128, 8, 24
+    g = torch.Generator().manual_seed(3)
+    prefix = torch.randint(2500, 4500, (bs,), generator=g).tolist()
+    pb = _backend_problem(Hq, Hkv, D, prefix, [n] * bs, seed=79)
+    parts = []
+    for P in prefix:
+        m = torch.zeros(n, P + n, dtype=torch.bool)
+        m[:, :P] = True
+        tri = torch.tril(torch.rand(n, n, generator=g) < 0.5)
+        tri[torch.arange(n), torch.arange(n)] = True
+        m[:, P:] = tri
+        parts.append(m.reshape(-1))
+    mask = torch.cat(parts)
+    indptr = torch.tensor([0] + [n * (P + n) for P in prefix]).cumsum(0)
+    fb = ForwardBatch(forward_mode=ForwardMode.TARGET_VERIFY, batch_size=bs, req_pool_indices=pb.rpi.cuda(),
+                      seq_lens=torch.tensor(prefix, dtype=torch.int32, device="cuda"), out_cache_loc=pb.loc.cuda(),
+                      seq_lens_sum=sum(prefix), spec_info=SimpleNamespace(draft_token_num=n, custom_mask=mask.cuda()))
+    be = pb.backend
+    be.init_forward_metadata(fb)
+    assert be._ext_splits > 1 and be._ext_tiles == bs and bs * Hkv > be.sm_count
+    layer = RadixAttention(Hq, D, D ** -0.5, Hkv, 0)
+    out = layer(pb.q.cuda().reshape(pb.T, -1), pb.k_new.cuda().reshape(pb.T, -1), pb.v_new.cuda().reshape(pb.T, -1), fb, be)
+    torch.cuda.synchronize()
+    want = ref.extend_ref(pb.q, pb.kp, pb.vp, pb.rtt, pb.rpi, torch.tensor(prefix), torch.tensor([n] * bs), D ** -0.5,
+                          custom_mask=mask.to(torch.uint8), mask_indptr=indptr)
+    assert_close_scaled(out.float().cpu().view(pb.T, Hq, D), want, "backend verify, tail-only split")
